@@ -1,0 +1,151 @@
+/* b200ddp.h — C ABI of libb200ddp.so: the B200 (sm_100a) kernels behind the DDP training step of
+ * annalena-k/tutorial-torch-distributed-data-parallel.
+ *
+ * The reference has no FFI of its own: its hot path is Python calling torch / torchvision / NCCL
+ * (SURVEY.md 8(b)). Each entry point below therefore cites the reference call site it serves and the
+ * upstream (torch 2.11.0, torchvision 0.26.0, NCCL 2.28.9) routine it replaces. INTEGRATION.md shows
+ * the ctypes binding the Python layer uses.
+ *
+ * Conventions
+ *   - plain C types only; every pointer is a BORROWED device pointer unless stated otherwise;
+ *   - `device` is the CUDA ordinal the buffers live on, `stream` a cudaStream_t passed as void*;
+ *   - all work is stream ordered and asynchronous; nothing synchronises the device;
+ *   - return value 0 = success; otherwise b200ddp_last_error() (thread local) describes the failure;
+ *     1 = invalid argument, 2 = not initialised, 1000+e = cudaError_t e, 2000+r = ncclResult_t r,
+ *     3000+r = CUresult r;
+ *   - the library never allocates or frees device memory: scratch / workspace buffers are provided
+ *     by the caller, their sizes come from the *_bytes() queries;
+ *   - entry points may be called from any host thread (autograd runs hooks on worker threads).
+ */
+#ifndef B200DDP_H_
+#define B200DDP_H_
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---- library ---------------------------------------------------------------------------------- */
+const char* b200ddp_last_error(void);
+int b200ddp_version(void);
+/* Number of CUDA kernels this library has launched in this process (evidence for bench `gpu_launches`). */
+unsigned long long b200ddp_launch_count(void);
+int b200ddp_device_info(int device, int* sm_count, int* cc_major, int* cc_minor);
+
+/* ---- O1: optimizer ---------------------------------------------------------------------------- */
+/* Replaces torch.optim.Adam._multi_tensor_adam (torch/optim/adam.py:554-800), reached from
+ * reference multi-GPU-training-torch.py:126 `optimizer.step()` and :249 `optim.Adam(..., lr=0.001)`.
+ * One pass over flat arenas: p,g,m,v of n floats (16-byte aligned). `step` is the 1-based step count
+ * AFTER increment. grad_scale_dev (nullable): device scalar multiplied into g first. */
+int b200ddp_adam_step_flat(float* p, const float* g, float* m, float* v, long long n, double lr, double beta1,
+                           double beta2, double eps, double weight_decay, long long step,
+                           const float* grad_scale_dev, int device, void* stream);
+
+/* ---- R1: bucket plan (host only) ---------------------------------------------------------------- */
+/* Replaces c10d::compute_bucket_assignment_by_size (torch reducer.hpp:592-598; called from
+ * torch/nn/parallel/distributed.py:1237-1244 when reference :245 constructs DDP). nbytes[i] = size of
+ * tensor i in ready order, keys[i] (nullable) = dtype/device key, caps = byte caps (e.g. {1 MiB, 25 MiB}).
+ * Writes bucket_of[i] and *nbuckets. */
+int b200ddp_plan_buckets(const long long* nbytes, const int* keys, int n, const long long* caps, int ncaps,
+                         int* bucket_of, int* nbuckets);
+
+/* ---- R2/R3: pack, scale, clip before aggregation ------------------------------------------------ */
+/* dst = clamp(src, +-clip_value) * scale (clip_value <= 0: no clamp); dst may alias src.
+ * Replaces Reducer::mark_variable_ready_dense's grad*1/ws copy (reducer.hpp:276) and
+ * torch.nn.utils.clip_grad_value_ (clip_grad.py:291-299) placed before the all-reduce (README.md:92-95). */
+int b200ddp_pack_scale_clip(float* dst, const float* src, long long n, float scale, float clip_value,
+                            int nan_to_zero, int device, void* stream);
+/* g *= *coef_dev; no memory traffic when *coef_dev == 1; exact_zero: *coef_dev == 0 stores zeros. */
+int b200ddp_scale_by_device_scalar(float* g, long long n, const float* coef_dev, int exact_zero, int device,
+                                   void* stream);
+/* out_sq[0] (+)= sum(g^2). Local part of clip_grad_norm_ (clip_grad.py:50-118). scratch: 256-byte
+ * aligned, >= b200ddp_sqnorm_scratch_bytes() bytes, its first 4 bytes zero before the first call. */
+long long b200ddp_sqnorm_scratch_bytes(void);
+int b200ddp_sqnorm(const float* g, long long n, float* out_sq, int accumulate, void* scratch,
+                   long long scratch_bytes, int device, void* stream);
+/* coef = min(1, max_norm / (sqrt(*sq_dev) + 1e-6)) (clip_grad.py:165-169); nonfinite_policy 0 = stock
+ * (NaN propagates), 1 = coef 0 (this rank contributes nothing). norm_out_dev nullable. */
+int b200ddp_clip_coef(const float* sq_dev, float max_norm, int nonfinite_policy, float* coef_out_dev,
+                      float* norm_out_dev, int device, void* stream);
+
+/* ---- R4: collectives (NCCL over NVLink 5 / NVSwitch) ------------------------------------------- */
+/* Replaces ProcessGroupNCCL::allreduce / allgather / broadcast as used by c10d::Reducer
+ * (reducer.hpp:276-286), SyncBatchNorm (_functions.py:74-76,165) and DDP's parameter broadcast
+ * (distributed.py:883-890). The comm handle owns an ncclComm_t, a high-priority communication stream
+ * and the events that order it against the caller's compute stream. */
+int b200ddp_nccl_load(const char* libnccl_path_or_null);
+int b200ddp_nccl_version(int* version);
+int b200ddp_comm_unique_id(void* out, int nbytes /* >= 128 */);
+int b200ddp_comm_create(void** handle_out, const void* unique_id, int rank, int nranks, int device);
+int b200ddp_comm_destroy(void* handle);
+int b200ddp_comm_rank(void* handle, int* rank, int* nranks);
+/* In place sum over ranks of (premul * buf) on the caller's stream. */
+int b200ddp_comm_allreduce(void* handle, float* buf, long long n, float premul, void* stream);
+int b200ddp_comm_allgather(void* handle, const float* send, float* recv, long long n_per_rank, void* stream);
+int b200ddp_comm_broadcast(void* handle, void* buf, long long nbytes, int root, void* stream);
+/* Bucket all-reduce overlapped with backward: valid-at = current tail of compute_stream; runs on the
+ * handle's communication stream; join makes compute_stream wait for every launched bucket. */
+int b200ddp_bucket_reduce_launch(void* handle, float* buf, long long n, float premul, void* compute_stream);
+int b200ddp_bucket_reduce_join(void* handle, void* compute_stream);
+
+/* ---- F1/F2/F3: Linear layers --------------------------------------------------------------------- */
+/* Replace nn.Linear forward/backward (cuBLAS sgemm) + nn.ReLU + nn.Dropout of torchvision
+ * alexnet.py:38-43 and the head data_and_toy_model.py:44, reached from reference :121 / :125.
+ * Layouts: x [B][K], w [N][K] (torch Linear weight), y / dz [B][N], row-major fp32.
+ * mode 0 = strict fp32 SIMT, mode 1 = TF32 tcgen05 tensor cores. N <= 16 uses the head kernels.
+ * Epilogue of fwd: y = dropout(relu(x w^T + bias)); gate[b][n] (nullable) = 0 off, 1 on, 2 on*1/(1-p).
+ * ws: workspace of b200ddp_linear_workspace_bytes(B,N,K) bytes for the split-K partials. */
+long long b200ddp_linear_workspace_bytes(int B, int N, int K);
+int b200ddp_linear_fwd(const float* x, const float* w, const float* bias, float* y, unsigned char* gate, int B, int N,
+                       int K, int relu, float dropout_p, unsigned long long seed, int mode, void* ws,
+                       long long ws_bytes, int device, void* stream);
+int b200ddp_linear_bwd_dx(const float* dz, const float* w, float* dx, int B, int N, int K, int mode, void* ws,
+                          long long ws_bytes, int device, void* stream);
+/* dw [N][K] = dz^T x (written, not accumulated); db [N] (nullable) = column sums of dz. */
+int b200ddp_linear_bwd_dw(const float* dz, const float* x, float* dw, float* db, int B, int N, int K, int mode,
+                          int device, void* stream);
+/* dz = dy * gate (0 / 1 / 1/(1-p)); db[n] (nullable) = sum_b dz[b][n]; dz nullable. */
+int b200ddp_gate_bias_bwd(const float* dy, const unsigned char* gate, float dropout_p, float* dz, float* db, int B,
+                          int N, int device, void* stream);
+
+/* ---- F3: loss ---------------------------------------------------------------------------------------- */
+/* Replaces nn.CrossEntropyLoss() (reference :248,:122): loss[0] = mean CE, dlogits (nullable) =
+ * (softmax - onehot)/B. labels int64. err_flag_dev (nullable) set to 1 on an out-of-range label. */
+int b200ddp_softmax_ce(const float* logits, const long long* labels, float* loss, float* dlogits, int B, int C,
+                       int* err_flag_dev, int device, void* stream);
+
+/* ---- C6: activations / pooling / dropout ------------------------------------------------------------ */
+/* Replace nn.ReLU + nn.MaxPool2d(3,2) (alexnet.py:23-24,26-27,33-34), nn.ReLU (:29,:31) and
+ * nn.Dropout (:38,:41). NCHW fp32. idx: one byte per output, window slot 0..8, 255 = ReLU closed. */
+int b200ddp_relu_maxpool_fwd(const float* x, float* y, unsigned char* idx, int B, int C, int H, int W, int relu,
+                             int device, void* stream);
+int b200ddp_relu_maxpool_bwd(const float* dy, const unsigned char* idx, float* dx, int B, int C, int H, int W,
+                             int device, void* stream);
+int b200ddp_relu_fwd(float* x, long long n, int device, void* stream);
+int b200ddp_relu_bwd(const float* dy, const float* y, float* dx, long long n, int device, void* stream);
+int b200ddp_dropout_fwd(const float* x, float* y, unsigned char* gate, long long n, float p, unsigned long long seed,
+                        int device, void* stream);
+
+/* ---- B1: SyncBatchNorm --------------------------------------------------------------------------------- */
+/* Replace aten::batch_norm_stats / _gather_stats_with_counts / _elemt / _backward_reduce /
+ * _backward_elemt as called by torch/nn/modules/_functions.py:7-209 (README.md:79-81 of the reference).
+ * x,y,dy,dx: [B][C][HW] fp32. scratch: 256-byte aligned, b200ddp_bn_scratch_bytes(B,C) bytes, zeroed
+ * once before first use (the kernels reset their tickets). y_relu (nullable): post-ReLU output, masks dy. */
+long long b200ddp_bn_scratch_bytes(int B, int C);
+int b200ddp_bn_stats(const float* x, int B, int C, int HW, float eps, float* mean, float* invstd, void* scratch,
+                     long long scratch_bytes, int device, void* stream);
+int b200ddp_bn_gather_stats(const float* all_stats /* [world][2C+1] */, int world, int C, float eps, float momentum,
+                            float* running_mean, float* running_var, float* mean, float* invstd, int device,
+                            void* stream);
+int b200ddp_bn_elemt(const float* x, const float* mean, const float* invstd, const float* weight, const float* bias,
+                     float* y, int B, int C, int HW, int relu, int device, void* stream);
+int b200ddp_bn_bwd_reduce(const float* dy, const float* x, const float* y_relu, const float* mean, const float* invstd,
+                          int B, int C, int HW, float* sum_dy, float* sum_dy_xmu, float* grad_weight, float* grad_bias,
+                          void* scratch, long long scratch_bytes, int device, void* stream);
+int b200ddp_bn_bwd_elemt(const float* dy, const float* x, const float* y_relu, const float* mean, const float* invstd,
+                         const float* weight, const float* sum_dy, const float* sum_dy_xmu, float inv_count, float* dx,
+                         int B, int C, int HW, int device, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200DDP_H_ */

@@ -1,0 +1,155 @@
+"""ctypes binding of libb200ddp.so (the C ABI declared in include/b200ddp.h).
+
+There is no CPU implementation behind these calls: if the shared library is missing, or a call is
+made for tensors that are not on a CUDA device, the caller gets an exception (no
+fallback for kernels).
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+import threading
+from ctypes import (POINTER, c_char_p, c_double, c_float, c_int, c_longlong, c_ulonglong, c_void_p)
+
+import torch
+
+from . import _build
+
+_LIB = None
+_LOCK = threading.Lock()
+
+
+class B200Error(RuntimeError):
+    pass
+
+
+_P = c_void_p  # every device pointer travels as void*
+
+_PROTOS = {
+    "b200ddp_last_error": (c_char_p, []),
+    "b200ddp_version": (c_int, []),
+    "b200ddp_launch_count": (c_ulonglong, []),
+    "b200ddp_device_info": (c_int, [c_int, POINTER(c_int), POINTER(c_int), POINTER(c_int)]),
+    "b200ddp_adam_step_flat": (c_int, [_P, _P, _P, _P, c_longlong, c_double, c_double, c_double, c_double, c_double,
+                                       c_longlong, _P, c_int, _P]),
+    "b200ddp_plan_buckets": (c_int, [POINTER(c_longlong), POINTER(c_int), c_int, POINTER(c_longlong), c_int,
+                                     POINTER(c_int), POINTER(c_int)]),
+    "b200ddp_pack_scale_clip": (c_int, [_P, _P, c_longlong, c_float, c_float, c_int, c_int, _P]),
+    "b200ddp_scale_by_device_scalar": (c_int, [_P, c_longlong, _P, c_int, c_int, _P]),
+    "b200ddp_sqnorm_scratch_bytes": (c_longlong, []),
+    "b200ddp_sqnorm": (c_int, [_P, c_longlong, _P, c_int, _P, c_longlong, c_int, _P]),
+    "b200ddp_clip_coef": (c_int, [_P, c_float, c_int, _P, _P, c_int, _P]),
+    "b200ddp_nccl_load": (c_int, [c_char_p]),
+    "b200ddp_nccl_version": (c_int, [POINTER(c_int)]),
+    "b200ddp_comm_unique_id": (c_int, [_P, c_int]),
+    "b200ddp_comm_create": (c_int, [POINTER(c_void_p), _P, c_int, c_int, c_int]),
+    "b200ddp_comm_destroy": (c_int, [_P]),
+    "b200ddp_comm_rank": (c_int, [_P, POINTER(c_int), POINTER(c_int)]),
+    "b200ddp_comm_allreduce": (c_int, [_P, _P, c_longlong, c_float, _P]),
+    "b200ddp_comm_allgather": (c_int, [_P, _P, _P, c_longlong, _P]),
+    "b200ddp_comm_broadcast": (c_int, [_P, _P, c_longlong, c_int, _P]),
+    "b200ddp_bucket_reduce_launch": (c_int, [_P, _P, c_longlong, c_float, _P]),
+    "b200ddp_bucket_reduce_join": (c_int, [_P, _P]),
+    "b200ddp_linear_workspace_bytes": (c_longlong, [c_int, c_int, c_int]),
+    "b200ddp_linear_fwd": (c_int, [_P, _P, _P, _P, _P, c_int, c_int, c_int, c_int, c_float, c_ulonglong, c_int, _P,
+                                   c_longlong, c_int, _P]),
+    "b200ddp_linear_bwd_dx": (c_int, [_P, _P, _P, c_int, c_int, c_int, c_int, _P, c_longlong, c_int, _P]),
+    "b200ddp_linear_bwd_dw": (c_int, [_P, _P, _P, _P, c_int, c_int, c_int, c_int, c_int, _P]),
+    "b200ddp_gate_bias_bwd": (c_int, [_P, _P, c_float, _P, _P, c_int, c_int, c_int, _P]),
+    "b200ddp_softmax_ce": (c_int, [_P, _P, _P, _P, c_int, c_int, _P, c_int, _P]),
+    "b200ddp_relu_maxpool_fwd": (c_int, [_P, _P, _P, c_int, c_int, c_int, c_int, c_int, c_int, _P]),
+    "b200ddp_relu_maxpool_bwd": (c_int, [_P, _P, _P, c_int, c_int, c_int, c_int, c_int, _P]),
+    "b200ddp_relu_fwd": (c_int, [_P, c_longlong, c_int, _P]),
+    "b200ddp_relu_bwd": (c_int, [_P, _P, _P, c_longlong, c_int, _P]),
+    "b200ddp_dropout_fwd": (c_int, [_P, _P, _P, c_longlong, c_float, c_ulonglong, c_int, _P]),
+    "b200ddp_bn_scratch_bytes": (c_longlong, [c_int, c_int]),
+    "b200ddp_bn_stats": (c_int, [_P, c_int, c_int, c_int, c_float, _P, _P, _P, c_longlong, c_int, _P]),
+    "b200ddp_bn_gather_stats": (c_int, [_P, c_int, c_int, c_float, c_float, _P, _P, _P, _P, c_int, _P]),
+    "b200ddp_bn_elemt": (c_int, [_P, _P, _P, _P, _P, _P, c_int, c_int, c_int, c_int, c_int, _P]),
+    "b200ddp_bn_bwd_reduce": (c_int, [_P, _P, _P, _P, _P, c_int, c_int, c_int, _P, _P, _P, _P, _P, c_longlong, c_int,
+                                      _P]),
+    "b200ddp_bn_bwd_elemt": (c_int, [_P, _P, _P, _P, _P, _P, _P, _P, c_float, _P, c_int, c_int, c_int, c_int, _P]),
+}
+
+
+def lib_path() -> str:
+    return _build.LIB_PATH
+
+
+def load(build_if_missing: bool = False):
+    """Load libb200ddp.so (once). Raises B200Error when it is absent: there is no CPU fallback."""
+    global _LIB
+    if _LIB is not None:
+        return _LIB
+    with _LOCK:
+        if _LIB is not None:
+            return _LIB
+        path = lib_path()
+        if not os.path.exists(path):
+            if build_if_missing:
+                _build.build()
+            else:
+                raise B200Error(
+                    f"{path} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'`. "
+                    "b200ddp has no CPU/eager fallback for its CUDA kernels.")
+        l = ctypes.CDLL(path, mode=ctypes.RTLD_GLOBAL)
+        for name, (res, args) in _PROTOS.items():
+            fn = getattr(l, name)  # AttributeError here means the .so is stale w.r.t. the header
+            fn.restype = res
+            fn.argtypes = args
+        _LIB = l
+    return _LIB
+
+
+def is_loaded() -> bool:
+    return _LIB is not None
+
+
+def last_error() -> str:
+    return load().b200ddp_last_error().decode(errors="replace")
+
+
+def check(rc: int, what: str = "") -> None:
+    if rc != 0:
+        raise B200Error(f"libb200ddp {what} failed (code {rc}): {last_error()}")
+
+
+def launch_count() -> int:
+    return int(load().b200ddp_launch_count()) if _LIB is not None else 0
+
+
+def ptr(t) -> int | None:
+    """Device pointer of a tensor (None passes NULL)."""
+    return None if t is None else t.data_ptr()
+
+
+def cur_stream(device) -> int:
+    return torch.cuda.current_stream(device).cuda_stream
+
+
+def dev_index(t) -> int:
+    if not t.is_cuda:
+        raise B200Error("b200ddp kernels need CUDA tensors (no CPU fallback); got a tensor on " + str(t.device))
+    return t.device.index if t.device.index is not None else torch.cuda.current_device()
+
+
+def f32c(t, name: str = "tensor"):
+    """Contiguous fp32 CUDA tensor or an exception (the kernels do not convert)."""
+    if t.dtype != torch.float32:
+        raise B200Error(f"{name}: expected float32, got {t.dtype}")
+    return t if t.is_contiguous() else t.contiguous()
+
+
+_WORKSPACES: dict = {}
+
+
+def workspace(device, nbytes: int, tag: str = "ws", zero: bool = False):
+    """Per-(device, tag) scratch tensor, grown on demand and reused (the C ABI never allocates)."""
+    key = (str(device), tag)
+    buf = _WORKSPACES.get(key)
+    if buf is None or buf.numel() < nbytes:
+        n = max(int(nbytes), 256)
+        buf = torch.zeros(n, dtype=torch.uint8, device=device) if zero else torch.empty(n, dtype=torch.uint8,
+                                                                                        device=device)
+        _WORKSPACES[key] = buf
+    return buf

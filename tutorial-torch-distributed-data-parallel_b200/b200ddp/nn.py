@@ -1,0 +1,439 @@
+"""Layers of the toy model as autograd Functions over the C ABI (F1-F3, C6, B1).
+
+Module names and parameter layouts follow torch / torchvision so state dicts interchange:
+`Linear` keeps `weight [out,in]` and `bias [out]` (torchvision alexnet.py:39,42 and
+data_and_toy_model.py:44), `SyncBatchNorm` keeps `weight, bias, running_mean, running_var,
+num_batches_tracked` (torch/nn/modules/batchnorm.py:745-842) and
+`SyncBatchNorm.convert_sync_batchnorm` mirrors batchnorm.py:844-905 (README.md:79-81 of the
+reference prescribes it before wrapping in DDP).
+
+There is no CPU path: these Functions raise for non-CUDA tensors.
+"""
+from __future__ import annotations
+
+from typing import Optional
+
+import torch
+import torch.distributed as dist
+from torch import nn
+from torch.nn.modules.batchnorm import _BatchNorm
+
+from . import _lib
+from .comm import get_comm
+
+MODE_FP32 = 0   # strict fp32 SIMT kernels (parity against the reference's fp32 sgemm)
+MODE_TF32 = 1   # tcgen05 TF32 tensor cores, fp32 accumulate (throughput)
+
+_seed_counter = [0]
+
+
+def _next_seed() -> int:
+    """Dropout seed drawn from torch's CPU generator: follows torch.manual_seed, differs per call."""
+    return int(torch.randint(0, 2 ** 62, (1,), dtype=torch.int64).item())
+
+
+def _mode_id(mode) -> int:
+    if mode in (MODE_FP32, "fp32", "strict"):
+        return MODE_FP32
+    if mode in (MODE_TF32, "tf32"):
+        return MODE_TF32
+    raise ValueError(f"unknown compute mode {mode!r} (use 'fp32' or 'tf32')")
+
+
+# ---------------------------------------------------------------------------------------------------------
+# Linear (+ bias + ReLU + dropout)
+# ---------------------------------------------------------------------------------------------------------
+class _LinearFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, weight, bias, relu, p, seed, mode):
+        L = _lib.load()
+        dev = _lib.dev_index(x)
+        x2 = _lib.f32c(x.reshape(-1, x.shape[-1]), "input")
+        w = _lib.f32c(weight, "weight")
+        B, K = x2.shape
+        N = w.shape[0]
+        if w.shape[1] != K:
+            raise ValueError(f"Linear: input features {K} != weight in_features {w.shape[1]}")
+        y = torch.empty((B, N), dtype=torch.float32, device=x.device)
+        need_gate = bool(relu) or p > 0.0
+        gate = torch.empty((B, N), dtype=torch.uint8, device=x.device) if need_gate else None
+        ws_bytes = int(L.b200ddp_linear_workspace_bytes(B, N, K))
+        ws = _lib.workspace(x.device, ws_bytes, "linear")
+        st = _lib.cur_stream(x.device)
+        _lib.check(L.b200ddp_linear_fwd(x2.data_ptr(), w.data_ptr(), _lib.ptr(bias), y.data_ptr(), _lib.ptr(gate),
+                                        B, N, K, int(bool(relu)), float(p), int(seed), mode, ws.data_ptr(),
+                                        ws.numel(), dev, st), "linear_fwd")
+        ctx.save_for_backward(x2, w, gate)
+        ctx.weight_param = weight
+        ctx.has_bias = bias is not None
+        ctx.bias_param = bias
+        ctx.p = float(p)
+        ctx.mode = mode
+        ctx.in_shape = x.shape
+        return y.view(*x.shape[:-1], N)
+
+    @staticmethod
+    def backward(ctx, dy):
+        L = _lib.load()
+        x2, w, gate = ctx.saved_tensors
+        dev = _lib.dev_index(x2)
+        st = _lib.cur_stream(x2.device)
+        B, K = x2.shape
+        N = w.shape[0]
+        dy2 = _lib.f32c(dy.reshape(B, N), "grad_output")
+        need_db = ctx.has_bias and ctx.needs_input_grad[2]
+        db = _grad_target(ctx.bias_param, (N,), x2.device) if need_db else None
+        if gate is not None:
+            dz = torch.empty_like(dy2)
+            _lib.check(L.b200ddp_gate_bias_bwd(dy2.data_ptr(), gate.data_ptr(), ctx.p, dz.data_ptr(), _lib.ptr(db),
+                                               B, N, dev, st), "gate_bias_bwd")
+            db_done = True
+        else:
+            dz = dy2
+            db_done = False
+        dx = None
+        if ctx.needs_input_grad[0]:
+            dx = torch.empty((B, K), dtype=torch.float32, device=x2.device)
+            ws_bytes = int(L.b200ddp_linear_workspace_bytes(B, N, K))
+            ws = _lib.workspace(x2.device, ws_bytes, "linear")
+            _lib.check(L.b200ddp_linear_bwd_dx(dz.data_ptr(), w.data_ptr(), dx.data_ptr(), B, N, K, ctx.mode,
+                                               ws.data_ptr(), ws.numel(), dev, st), "linear_bwd_dx")
+            dx = dx.view(ctx.in_shape)
+        dw = None
+        if ctx.needs_input_grad[1]:
+            dw = _grad_target(ctx.weight_param, (N, K), x2.device)
+            _lib.check(L.b200ddp_linear_bwd_dw(dz.data_ptr(), x2.data_ptr(), dw.data_ptr(),
+                                               None if db_done else _lib.ptr(db), B, N, K, ctx.mode, dev, st),
+                       "linear_bwd_dw")
+        elif need_db and not db_done:
+            _lib.check(L.b200ddp_gate_bias_bwd(dz.data_ptr(), None, 0.0, None, db.data_ptr(), B, N, dev, st),
+                       "bias_bwd")
+        return dx, dw, db, None, None, None, None
+
+
+def _grad_target(param, shape, device) -> torch.Tensor:
+    """Where a wgrad kernel should write: straight into the parameter's arena slice when autograd will
+    adopt the tensor as `.grad` (no accumulation pending), else a fresh buffer autograd adds up."""
+    slot = getattr(param, "_b200_slot", None) if param is not None else None
+    if slot is not None and param.grad is None:
+        return slot[0].grad_view(slot[1])
+    return torch.empty(shape, dtype=torch.float32, device=device)
+
+
+class Linear(nn.Linear):
+    """nn.Linear with the following ReLU and Dropout of the AlexNet classifier folded into its epilogue."""
+
+    def __init__(self, in_features: int, out_features: int, bias: bool = True, relu: bool = False,
+                 dropout: float = 0.0, mode="tf32", device=None, dtype=None) -> None:
+        super().__init__(in_features, out_features, bias=bias, device=device, dtype=dtype)
+        self.relu = bool(relu)
+        self.dropout = float(dropout)
+        self.mode = _mode_id(mode)
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        p = self.dropout if self.training else 0.0
+        seed = _next_seed() if p > 0.0 else 0
+        return _LinearFn.apply(x, self.weight, self.bias, self.relu, p, seed, self.mode)
+
+    def extra_repr(self) -> str:
+        return super().extra_repr() + f", relu={self.relu}, dropout={self.dropout}, mode={self.mode}"
+
+
+# ---------------------------------------------------------------------------------------------------------
+# softmax cross-entropy
+# ---------------------------------------------------------------------------------------------------------
+class _CrossEntropyFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, logits, labels):
+        L = _lib.load()
+        dev = _lib.dev_index(logits)
+        z = _lib.f32c(logits, "logits")
+        if z.dim() != 2:
+            raise ValueError("CrossEntropyLoss expects [batch, classes] logits")
+        if labels.dtype != torch.int64:
+            raise TypeError("CrossEntropyLoss expects int64 class indices")
+        y = labels.contiguous()
+        B, C = z.shape
+        loss = torch.empty((), dtype=torch.float32, device=z.device)
+        dlogits = torch.empty_like(z)
+        _lib.check(L.b200ddp_softmax_ce(z.data_ptr(), y.data_ptr(), loss.data_ptr(), dlogits.data_ptr(), B, C, None,
+                                        dev, _lib.cur_stream(z.device)), "softmax_ce")
+        ctx.save_for_backward(dlogits)
+        return loss
+
+    @staticmethod
+    def backward(ctx, gout):
+        (dlogits,) = ctx.saved_tensors
+        L = _lib.load()
+        g = gout.to(torch.float32).reshape(1).contiguous()
+        out = dlogits.clone() if dlogits.data_ptr() % 16 else dlogits
+        _lib.check(L.b200ddp_scale_by_device_scalar(out.data_ptr(), out.numel(), g.data_ptr(), 0,
+                                                    _lib.dev_index(out), _lib.cur_stream(out.device)), "ce_bwd")
+        return out, None
+
+
+class CrossEntropyLoss(nn.Module):
+    """Mean softmax cross-entropy over the batch (nn.CrossEntropyLoss() defaults, reference :248)."""
+
+    def forward(self, logits: torch.Tensor, labels: torch.Tensor) -> torch.Tensor:
+        return _CrossEntropyFn.apply(logits, labels)
+
+
+# ---------------------------------------------------------------------------------------------------------
+# ReLU, ReLU+MaxPool(3,2), Dropout
+# ---------------------------------------------------------------------------------------------------------
+class _ReluMaxPoolFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, relu):
+        L = _lib.load()
+        x = _lib.f32c(x, "input")
+        B, C, H, W = x.shape
+        OH, OW = (H - 3) // 2 + 1, (W - 3) // 2 + 1
+        y = torch.empty((B, C, OH, OW), dtype=torch.float32, device=x.device)
+        idx = torch.empty((B, C, OH, OW), dtype=torch.uint8, device=x.device)
+        _lib.check(L.b200ddp_relu_maxpool_fwd(x.data_ptr(), y.data_ptr(), idx.data_ptr(), B, C, H, W, int(relu),
+                                              _lib.dev_index(x), _lib.cur_stream(x.device)), "relu_maxpool_fwd")
+        ctx.save_for_backward(idx)
+        ctx.in_shape = (B, C, H, W)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        L = _lib.load()
+        (idx,) = ctx.saved_tensors
+        B, C, H, W = ctx.in_shape
+        dy = _lib.f32c(dy, "grad_output")
+        dx = torch.empty(ctx.in_shape, dtype=torch.float32, device=dy.device)
+        _lib.check(L.b200ddp_relu_maxpool_bwd(dy.data_ptr(), idx.data_ptr(), dx.data_ptr(), B, C, H, W,
+                                              _lib.dev_index(dy), _lib.cur_stream(dy.device)), "relu_maxpool_bwd")
+        return dx, None
+
+
+class ReLUMaxPool2d(nn.Module):
+    """nn.ReLU followed by nn.MaxPool2d(kernel_size=3, stride=2) in one pass (alexnet.py:23-24)."""
+
+    def __init__(self, relu: bool = True) -> None:
+        super().__init__()
+        self.relu = relu
+
+    def forward(self, x):
+        return _ReluMaxPoolFn.apply(x, self.relu)
+
+
+class _ReluFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x):
+        L = _lib.load()
+        if not x.is_contiguous():
+            x = x.contiguous()
+        _lib.f32c(x, "input")
+        _lib.check(L.b200ddp_relu_fwd(x.data_ptr(), x.numel(), _lib.dev_index(x), _lib.cur_stream(x.device)),
+                   "relu_fwd")
+        ctx.mark_dirty(x)
+        ctx.save_for_backward(x)
+        return x
+
+    @staticmethod
+    def backward(ctx, dy):
+        L = _lib.load()
+        (y,) = ctx.saved_tensors
+        dy = _lib.f32c(dy, "grad_output")
+        dx = torch.empty_like(dy)
+        _lib.check(L.b200ddp_relu_bwd(dy.data_ptr(), y.data_ptr(), dx.data_ptr(), dy.numel(), _lib.dev_index(dy),
+                                      _lib.cur_stream(dy.device)), "relu_bwd")
+        return dx
+
+
+class ReLU(nn.Module):
+    """In-place ReLU (nn.ReLU(inplace=True), alexnet.py:29,31)."""
+
+    def forward(self, x):
+        return _ReluFn.apply(x)
+
+
+class _DropoutFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, p, seed):
+        L = _lib.load()
+        x = _lib.f32c(x, "input")
+        y = torch.empty_like(x)
+        gate = torch.empty(x.shape, dtype=torch.uint8, device=x.device)
+        _lib.check(L.b200ddp_dropout_fwd(x.data_ptr(), y.data_ptr(), gate.data_ptr(), x.numel(), float(p), int(seed),
+                                         _lib.dev_index(x), _lib.cur_stream(x.device)), "dropout_fwd")
+        ctx.save_for_backward(gate)
+        ctx.p = float(p)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        L = _lib.load()
+        (gate,) = ctx.saved_tensors
+        dy = _lib.f32c(dy, "grad_output")
+        dx = torch.empty_like(dy)
+        n_last = dy.shape[-1]
+        rows = dy.numel() // n_last
+        _lib.check(L.b200ddp_gate_bias_bwd(dy.data_ptr(), gate.data_ptr(), ctx.p, dx.data_ptr(), None, rows, n_last,
+                                           _lib.dev_index(dy), _lib.cur_stream(dy.device)), "dropout_bwd")
+        return dx, None, None
+
+
+class Dropout(nn.Module):
+    """nn.Dropout(p) with a Philox mask that does not depend on launch geometry (alexnet.py:38,41)."""
+
+    def __init__(self, p: float = 0.5) -> None:
+        super().__init__()
+        if not 0.0 <= p < 1.0:
+            raise ValueError("dropout probability has to be in [0, 1)")
+        self.p = float(p)
+
+    def forward(self, x):
+        if not self.training or self.p == 0.0:
+            return x
+        return _DropoutFn.apply(x, self.p, _next_seed())
+
+
+# ---------------------------------------------------------------------------------------------------------
+# SyncBatchNorm
+# ---------------------------------------------------------------------------------------------------------
+class _SyncBatchNormFn(torch.autograd.Function):
+    """Restates torch/nn/modules/_functions.py:7-209 on top of the b200ddp_bn_* kernels."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias, running_mean, running_var, eps, momentum, comm, world, fuse_relu):
+        L = _lib.load()
+        x = _lib.f32c(x, "input")
+        dev, st = _lib.dev_index(x), _lib.cur_stream(x.device)
+        B, C = x.shape[0], x.shape[1]
+        HW = x.numel() // (B * C)
+        if B * HW == 1 and world < 2:
+            raise ValueError("Expected more than 1 value per channel when training")
+        scratch_bytes = int(L.b200ddp_bn_scratch_bytes(B, C))
+        scratch = _lib.workspace(x.device, scratch_bytes, "bn", zero=True)
+        stats = torch.empty(2 * C + 1, dtype=torch.float32, device=x.device)   # mean | invstd | count
+        _lib.check(L.b200ddp_bn_stats(x.data_ptr(), B, C, HW, float(eps), stats.data_ptr(),
+                                      stats.data_ptr() + 4 * C, scratch.data_ptr(), scratch.numel(), dev, st),
+                   "bn_stats")
+        stats[2 * C].fill_(float(B * HW))
+        if world > 1:
+            gathered = torch.empty(world * (2 * C + 1), dtype=torch.float32, device=x.device)
+            comm.allgather(stats, gathered)
+        else:
+            gathered = stats
+        mean = torch.empty(C, dtype=torch.float32, device=x.device)
+        invstd = torch.empty(C, dtype=torch.float32, device=x.device)
+        _lib.check(L.b200ddp_bn_gather_stats(gathered.data_ptr(), world, C, float(eps), float(momentum),
+                                             _lib.ptr(running_mean), _lib.ptr(running_var), mean.data_ptr(),
+                                             invstd.data_ptr(), dev, st), "bn_gather_stats")
+        y = torch.empty_like(x)
+        _lib.check(L.b200ddp_bn_elemt(x.data_ptr(), mean.data_ptr(), invstd.data_ptr(), _lib.ptr(weight),
+                                      _lib.ptr(bias), y.data_ptr(), B, C, HW, int(fuse_relu), dev, st), "bn_elemt")
+        ctx.save_for_backward(x, weight, mean, invstd, y if fuse_relu else None)
+        ctx.comm, ctx.world, ctx.count_local = comm, world, B * HW
+        ctx.weight_param, ctx.bias_param = weight, bias
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        L = _lib.load()
+        x, weight, mean, invstd, y_relu = ctx.saved_tensors
+        dy = _lib.f32c(dy, "grad_output")
+        dev, st = _lib.dev_index(x), _lib.cur_stream(x.device)
+        B, C = x.shape[0], x.shape[1]
+        HW = x.numel() // (B * C)
+        scratch_bytes = int(L.b200ddp_bn_scratch_bytes(B, C))
+        scratch = _lib.workspace(x.device, scratch_bytes, "bn", zero=True)
+        sums = torch.empty(2 * C, dtype=torch.float32, device=x.device)   # sum_dy | sum_dy_xmu
+        gw = _grad_target(ctx.weight_param, (C,), x.device) if weight is not None and ctx.needs_input_grad[1] else None
+        gb = _grad_target(ctx.bias_param, (C,), x.device) if ctx.bias_param is not None and ctx.needs_input_grad[2] else None
+        _lib.check(L.b200ddp_bn_bwd_reduce(dy.data_ptr(), x.data_ptr(), _lib.ptr(y_relu), mean.data_ptr(),
+                                           invstd.data_ptr(), B, C, HW, sums.data_ptr(), sums.data_ptr() + 4 * C,
+                                           _lib.ptr(gw), _lib.ptr(gb), scratch.data_ptr(), scratch.numel(), dev, st),
+                   "bn_bwd_reduce")
+        total = ctx.count_local
+        if ctx.world > 1:
+            ctx.comm.allreduce_(sums, 1.0)
+            total = ctx.count_local * ctx.world   # equal local batch sizes (DistributedSampler pads)
+        dx = None
+        if ctx.needs_input_grad[0]:
+            dx = torch.empty_like(x)
+            _lib.check(L.b200ddp_bn_bwd_elemt(dy.data_ptr(), x.data_ptr(), _lib.ptr(y_relu), mean.data_ptr(),
+                                              invstd.data_ptr(), _lib.ptr(weight), sums.data_ptr(),
+                                              sums.data_ptr() + 4 * C, 1.0 / float(total), dx.data_ptr(), B, C, HW,
+                                              dev, st), "bn_bwd_elemt")
+        return dx, gw, gb, None, None, None, None, None, None, None
+
+
+class SyncBatchNorm(_BatchNorm):
+    """Batch normalisation whose statistics span all ranks (drop-in for torch.nn.SyncBatchNorm).
+
+    `fuse_relu=True` additionally folds the ReLU that follows the layer in AlexNet-BN into the
+    normalisation kernel (and its mask into the backward kernels)."""
+
+    def __init__(self, num_features: int, eps: float = 1e-5, momentum: Optional[float] = 0.1, affine: bool = True,
+                 track_running_stats: bool = True, process_group=None, fuse_relu: bool = False, device=None,
+                 dtype=None) -> None:
+        super().__init__(num_features, eps, momentum, affine, track_running_stats, device=device, dtype=dtype)
+        self.process_group = process_group
+        self.fuse_relu = fuse_relu
+
+    def _check_input_dim(self, input) -> None:
+        if input.dim() < 2:
+            raise ValueError(f"expected at least 2D input (got {input.dim()}D input)")
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        self._check_input_dim(x)
+        if not x.is_cuda:
+            raise ValueError("SyncBatchNorm expected input tensor to be on GPU")   # as upstream batchnorm.py:800-809
+        if self.momentum is None:
+            eaf = 0.0
+        else:
+            eaf = self.momentum
+        if self.training and self.track_running_stats:
+            self.num_batches_tracked.add_(1)
+            if self.momentum is None:
+                eaf = 1.0 / float(self.num_batches_tracked.item())
+        use_batch_stats = self.training or (self.running_mean is None and self.running_var is None)
+        if not use_batch_stats:
+            # eval: running statistics, no communication (batchnorm.py:791-828)
+            L = _lib.load()
+            xc = _lib.f32c(x, "input")
+            B, C = xc.shape[0], xc.shape[1]
+            HW = xc.numel() // (B * C)
+            invstd = torch.rsqrt(self.running_var + self.eps)
+            y = torch.empty_like(xc)
+            _lib.check(L.b200ddp_bn_elemt(xc.data_ptr(), self.running_mean.data_ptr(), invstd.data_ptr(),
+                                          _lib.ptr(self.weight), _lib.ptr(self.bias), y.data_ptr(), B, C, HW,
+                                          int(self.fuse_relu), _lib.dev_index(xc), _lib.cur_stream(xc.device)),
+                       "bn_elemt")
+            return y
+        world = 1
+        comm = None
+        if dist.is_available() and dist.is_initialized():
+            world = dist.get_world_size(self.process_group)
+            if world > 1:
+                comm = get_comm(x.device, self.process_group)
+        rm = self.running_mean if self.track_running_stats else None
+        rv = self.running_var if self.track_running_stats else None
+        return _SyncBatchNormFn.apply(x, self.weight, self.bias, rm, rv, self.eps, eaf, comm, world, self.fuse_relu)
+
+    @classmethod
+    def convert_sync_batchnorm(cls, module: nn.Module, process_group=None) -> nn.Module:
+        """Recursively replace every BatchNorm*D child by SyncBatchNorm, sharing parameters and buffers."""
+        out = module
+        if isinstance(module, _BatchNorm) and not isinstance(module, SyncBatchNorm):
+            out = cls(module.num_features, module.eps, module.momentum, module.affine, module.track_running_stats,
+                      process_group)
+            if module.affine:
+                with torch.no_grad():
+                    out.weight = module.weight
+                    out.bias = module.bias
+            out.running_mean = module.running_mean
+            out.running_var = module.running_var
+            out.num_batches_tracked = module.num_batches_tracked
+            out.training = module.training
+            if hasattr(module, "qconfig"):
+                out.qconfig = module.qconfig
+        for name, child in module.named_children():
+            out.add_module(name, cls.convert_sync_batchnorm(child, process_group))
+        del module
+        return out

@@ -1,0 +1,265 @@
+"""R1-R4 — gradient bucketing, clip-before-aggregation and overlapped all-reduce.
+
+Plays the role of c10d::Reducer (torch reducer.hpp:45-584) behind the DistributedDataParallel
+wrapper that reference multi-GPU-training-torch.py:245 constructs:
+
+* bucket plan: parameters in reverse registration order (the order their gradients become ready,
+  SURVEY 3.2), greedy byte caps [1 MiB, 25 MiB] — computed by the native planner
+  (b200ddp_plan_buckets) which restates compute_bucket_assignment_by_size. Because the gradient arena
+  uses the same order, every bucket is one contiguous range reduced in place.
+* per-parameter post-accumulate-grad hooks mark readiness; a bucket whose parameters are all ready
+  is (clipped and) all-reduced on the communication stream while backward keeps running; buckets are
+  launched strictly in index order so all ranks issue identical NCCL sequences.
+* averaging is folded into the collective (PreMulSum 1/world_size) — no separate divide pass.
+* clipping happens on the LOCAL gradients before aggregation (reference README.md:92-95):
+  value mode clamps each bucket in place right before its all-reduce (overlap preserved);
+  norm mode accumulates per-bucket sums of squares during backward, computes
+  coef = min(1, c/(||g||+1e-6)) on the device when backward ends, scales and then reduces.
+
+With CPU tensors (gloo) the same host logic runs with torch ops in place of the kernels — that
+"plumbing mode" exists only so the control flow can be tested without a GPU.
+"""
+from __future__ import annotations
+
+import ctypes
+from typing import List, Optional
+
+import torch
+import torch.distributed as dist
+from torch.autograd import Variable
+
+from . import _lib
+from .arena import FlatArena
+
+MiB = 1 << 20
+
+
+def plan_buckets(nbytes: List[int], caps: List[int], keys: Optional[List[int]] = None) -> List[List[int]]:
+    """Bucket index lists for tensors of `nbytes` (native planner, host only)."""
+    L = _lib.load()
+    n = len(nbytes)
+    a = (ctypes.c_longlong * n)(*nbytes)
+    c = (ctypes.c_longlong * len(caps))(*caps)
+    k = (ctypes.c_int * n)(*keys) if keys is not None else None
+    out = (ctypes.c_int * max(n, 1))()
+    nb = ctypes.c_int(0)
+    _lib.check(L.b200ddp_plan_buckets(a, k, n, c, len(caps), out, ctypes.byref(nb)), "plan_buckets")
+    buckets: List[List[int]] = [[] for _ in range(nb.value)]
+    for i in range(n):
+        buckets[out[i]].append(i)
+    return buckets
+
+
+class _Bucket:
+    __slots__ = ("index", "members", "start", "end", "pending", "ready", "launched", "work")
+
+    def __init__(self, index: int, members: List[int], start: int, end: int) -> None:
+        self.index = index
+        self.members = members
+        self.start = start
+        self.end = end
+        self.pending = len(members)
+        self.ready = False
+        self.launched = False
+        self.work = None
+
+
+class Reducer:
+    def __init__(self, arena: FlatArena, process_group=None, bucket_cap_mb: float = 25.0,
+                 first_bucket_cap_mb: float = 1.0, clip_grad_value: Optional[float] = None,
+                 clip_grad_norm: Optional[float] = None, nonfinite: str = "propagate", comm=None) -> None:
+        if clip_grad_value is not None and clip_grad_norm is not None:
+            raise ValueError("choose clip_grad_value or clip_grad_norm, not both")
+        if nonfinite not in ("propagate", "zero"):
+            raise ValueError("nonfinite must be 'propagate' or 'zero'")
+        self.arena = arena
+        self.pg = process_group
+        self.cuda = arena.device.type == "cuda"
+        self.world = dist.get_world_size(process_group) if dist.is_available() and dist.is_initialized() else 1
+        self.comm = comm
+        self.clip_value = None if clip_grad_value is None else float(clip_grad_value)
+        self.clip_norm = None if clip_grad_norm is None else float(clip_grad_norm)
+        self.nonfinite_zero = nonfinite == "zero"
+        self.require_sync = True
+        self.last_local_norm: Optional[torch.Tensor] = None
+
+        params = arena.params
+        sizes = [p.numel() * 4 for p in params]
+        caps = [int(first_bucket_cap_mb * MiB), int(bucket_cap_mb * MiB)]
+        if self.cuda or _lib_available():
+            groups = plan_buckets(sizes, caps)
+        else:  # pragma: no cover - only when the .so has not been built on a CPU-only box
+            raise _lib.B200Error("libb200ddp.so is required for the bucket planner")
+        self.buckets: List[_Bucket] = []
+        for bi, members in enumerate(groups):
+            assert members == list(range(members[0], members[-1] + 1)), "buckets must be contiguous in arena order"
+            start, end = arena.span(members[0], members[-1])
+            self.buckets.append(_Bucket(bi, members, start, end))
+        self.bucket_of = [0] * len(params)
+        for b in self.buckets:
+            for i in b.members:
+                self.bucket_of[i] = b.index
+        self.next_bucket = 0
+        self._callback_queued = False
+        self._ready_order: List[int] = []
+        self.first_ready_order: Optional[List[int]] = None
+        if self.cuda:
+            dev = arena.device
+            self._sq = torch.zeros(1, dtype=torch.float32, device=dev)
+            self._coef = torch.ones(1, dtype=torch.float32, device=dev)
+            self._norm = torch.zeros(1, dtype=torch.float32, device=dev)
+            nbytes = int(_lib.load().b200ddp_sqnorm_scratch_bytes())
+            self._sq_scratch = torch.zeros(nbytes, dtype=torch.uint8, device=dev)
+        self._hooks = [p.register_post_accumulate_grad_hook(self._make_hook(i)) for i, p in enumerate(params)]
+
+    # ---- public ------------------------------------------------------------------------------------
+    def bucket_sizes_bytes(self) -> List[int]:
+        return [sum(self.arena.params[i].numel() * 4 for i in b.members) for b in self.buckets]
+
+    def bucket_param_indices(self) -> List[List[int]]:
+        return [list(b.members) for b in self.buckets]
+
+    def remove_hooks(self) -> None:
+        for h in self._hooks:
+            h.remove()
+        self._hooks = []
+
+    # ---- backward-time machinery ---------------------------------------------------------------------
+    def _make_hook(self, i: int):
+        def hook(param):
+            self._on_grad_ready(i, param)
+        return hook
+
+    def _reset(self) -> None:
+        for b in self.buckets:
+            b.pending = len(b.members)
+            b.ready = False
+            b.launched = False
+            b.work = None
+        self.next_bucket = 0
+        self._callback_queued = False
+        self._ready_order = []
+
+    def _on_grad_ready(self, i: int, param) -> None:
+        if not self.require_sync:
+            return
+        if not self._callback_queued:
+            self._reset()
+            self._callback_queued = True
+            if self.cuda and self.clip_norm is not None:
+                self._sq.zero_()
+            Variable._execution_engine.queue_callback(self._finalize)
+        self._ready_order.append(i)
+        arena = self.arena
+        if not arena.grad_in_arena(i):
+            # gradient was produced outside the arena (e.g. by a cuDNN wgrad): pack it into its slice
+            g = param.grad
+            view = arena.grad_view(i)
+            if self.cuda:
+                L = _lib.load()
+                src = g if g.is_contiguous() else g.contiguous()
+                _lib.check(L.b200ddp_pack_scale_clip(view.data_ptr(), src.data_ptr(), src.numel(), 1.0, 0.0, 0,
+                                                     _lib.dev_index(view), _lib.cur_stream(view.device)),
+                           "pack_scale_clip")
+            else:
+                view.copy_(g)
+            param.grad = view
+        b = self.buckets[self.bucket_of[i]]
+        b.pending -= 1
+        if b.pending == 0:
+            b.ready = True
+            while self.next_bucket < len(self.buckets) and self.buckets[self.next_bucket].ready:
+                self._bucket_ready(self.buckets[self.next_bucket])
+                self.next_bucket += 1
+
+    def _bucket_tensor(self, b: _Bucket) -> torch.Tensor:
+        return self.arena.g_flat[b.start:b.end]
+
+    def _bucket_ready(self, b: _Bucket) -> None:
+        t = self._bucket_tensor(b)
+        n = b.end - b.start
+        if self.cuda:
+            L = _lib.load()
+            dev, st = _lib.dev_index(t), _lib.cur_stream(t.device)
+            if self.clip_value is not None:
+                _lib.check(L.b200ddp_pack_scale_clip(t.data_ptr(), t.data_ptr(), n, 1.0, self.clip_value,
+                                                     1 if self.nonfinite_zero else 0, dev, st), "clip_value")
+            if self.clip_norm is not None:
+                _lib.check(L.b200ddp_sqnorm(t.data_ptr(), n, self._sq.data_ptr(), 1, self._sq_scratch.data_ptr(),
+                                            self._sq_scratch.numel(), dev, st), "sqnorm")
+                return  # all-reduce deferred until the full local norm is known (see _finalize)
+            self._launch_allreduce(b)
+        else:
+            if self.clip_value is not None:
+                if self.nonfinite_zero:
+                    torch.nan_to_num_(t, nan=0.0)
+                t.clamp_(-self.clip_value, self.clip_value)
+            if self.clip_norm is not None:
+                return
+            self._launch_allreduce(b)
+
+    def _launch_allreduce(self, b: _Bucket) -> None:
+        b.launched = True
+        if self.world == 1:
+            return
+        t = self._bucket_tensor(b)
+        if self.cuda:
+            self.comm.bucket_reduce_launch(t.data_ptr(), b.end - b.start, 1.0 / self.world, t.device)
+        else:
+            t.mul_(1.0 / self.world)
+            b.work = dist.all_reduce(t, group=self.pg, async_op=True)
+
+    def _finalize(self) -> None:
+        """Runs once when the autograd engine has finished this backward pass."""
+        try:
+            if not all(b.ready for b in self.buckets):
+                missing = [i for b in self.buckets if not b.ready for i in b.members
+                           if i not in self._ready_order]
+                raise RuntimeError(
+                    "b200ddp Reducer: backward finished but parameters "
+                    f"{missing} produced no gradient (unused parameters are not supported)")
+            if self.first_ready_order is None:
+                self.first_ready_order = list(self._ready_order)
+            if self.clip_norm is not None:
+                self._clip_by_norm_then_reduce()
+            if self.world > 1:
+                if self.cuda:
+                    self.comm.bucket_reduce_join(self.arena.device)
+                else:
+                    for b in self.buckets:
+                        if b.work is not None:
+                            b.work.wait()
+        finally:
+            self._callback_queued = False
+
+    def _clip_by_norm_then_reduce(self) -> None:
+        g = self.arena.g_flat
+        if self.cuda:
+            L = _lib.load()
+            dev, st = _lib.dev_index(g), _lib.cur_stream(g.device)
+            _lib.check(L.b200ddp_clip_coef(self._sq.data_ptr(), self.clip_norm, 1 if self.nonfinite_zero else 0,
+                                           self._coef.data_ptr(), self._norm.data_ptr(), dev, st), "clip_coef")
+            for b in self.buckets:
+                t = self._bucket_tensor(b)
+                _lib.check(L.b200ddp_scale_by_device_scalar(t.data_ptr(), b.end - b.start, self._coef.data_ptr(),
+                                                            1 if self.nonfinite_zero else 0, dev, st), "scale")
+                self._launch_allreduce(b)
+            self.last_local_norm = self._norm
+        else:
+            norm = torch.linalg.vector_norm(g)
+            coef = self.clip_norm / (norm + 1e-6)
+            if self.nonfinite_zero and not bool(torch.isfinite(norm)):
+                g.zero_()
+            else:
+                g.mul_(torch.clamp(coef, max=1.0))
+            self.last_local_norm = norm
+            for b in self.buckets:
+                self._launch_allreduce(b)
+
+
+def _lib_available() -> bool:
+    try:
+        _lib.load()
+        return True
+    except Exception:
+        return False

@@ -1,0 +1,61 @@
+// Private interface between the linear-layer entry points (linear.cu) and the two GEMM
+// engines: the strict-fp32 SIMT kernel (linear.cu) and the TF32 tcgen05/TMA kernel (gemm_tf32.cu).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "common.cuh"
+
+namespace b200 {
+
+// Fused epilogue applied to an output matrix stored row-major as [rows x cols] with leading
+// dimension ld: v = acc + bias[col]; relu; dropout (Philox keyed by row*ld+col); gate byte.
+struct Epilogue {
+  const float* bias = nullptr;      // per column, may be null
+  int relu = 0;
+  int dropout = 0;
+  uint32_t p_threshold = 0;         // keep iff philox >= p_threshold
+  float drop_scale = 1.f;           // 1/(1-p)
+  unsigned long long seed = 0;
+  unsigned char* gate = nullptr;    // optional [rows x cols] (same ld): 0 = off, 1 = on, 2 = on*drop_scale
+};
+
+__device__ __forceinline__ float apply_epilogue(float v, const Epilogue& ep, long long row, long long col,
+                                                long long ld) {
+  if (ep.bias) v += __ldg(ep.bias + col);
+  unsigned char gate = 1;
+  if (ep.relu && !(v > 0.f)) { v = 0.f; gate = 0; }
+  if (ep.dropout) {
+    if (dropout_keep(ep.seed, (uint64_t)(row * ld + col), ep.p_threshold)) {
+      v *= ep.drop_scale;
+      if (gate) gate = 2;
+    } else {
+      v = 0.f; gate = 0;
+    }
+  }
+  if (ep.gate) ep.gate[row * ld + col] = gate;
+  return v;
+}
+
+// TF32 tensor-core GEMM  D[m][n] = sum_r A(m,r) * B(n,r), written TRANSPOSED: out[n*ldo + m].
+//   a_mn_major = 0: A stored [M x R] (r contiguous, lda = row stride); 1: A stored [R x M] (m contiguous).
+//   b_mn_major likewise for B ([N x R] or [R x N]).
+// splits > 1 writes raw partials to ws[z][n][m] (ld = M) and the caller runs splitk_finalize.
+int tf32_gemm_launch(const float* A, long long lda, int a_mn_major, const float* B, long long ldb,
+                     int b_mn_major, int M, int N, int R, float* out, long long ldo, int splits, float* ws,
+                     const Epilogue& ep, cudaStream_t stream);
+
+// Number of K splits tf32_gemm_launch will really use for a request (no empty splits).
+inline int tf32_effective_splits(int R, int splits) {
+  const int total_kb = (R + 31) / 32;
+  if (splits < 1) splits = 1;
+  if (splits > total_kb) splits = total_kb;
+  const int per = (total_kb + splits - 1) / splits;
+  return (total_kb + per - 1) / per;
+}
+
+// out[row*ldo + col] = epilogue(sum_z ws[z][row][col]), ws slices are dense [rows x cols].
+int splitk_finalize_launch(const float* ws, int splits, int rows, int cols, float* out, long long ldo,
+                           const Epilogue& ep, cudaStream_t stream);
+
+}  // namespace b200

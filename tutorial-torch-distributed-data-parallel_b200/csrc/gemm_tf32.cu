@@ -1,0 +1,347 @@
+// F1 / F2 — TF32 tensor-core GEMM for the classifier's Linear layers, hand-written for sm_100a:
+// TMA (cp.async.bulk.tensor, 128B swizzle) -> shared memory ring -> tcgen05.mma kind::tf32 with
+// the fp32 accumulator in TMEM -> tcgen05.ld epilogue with bias / ReLU / dropout / gate folded in.
+//
+// The operands are the fp32 master weights and activations exactly as they sit in HBM: the tensor
+// core reads the top 19 bits of each fp32 word, so there is no conversion pass and no low-precision
+// copy of the 151 MB / 67 MB weight matrices (reference alexnet.py:39,42 run as fp32 cuBLAS sgemm;
+// at batch 128 these GEMMs are weight-streaming bound).
+//
+// Shape convention:  D[m][n] = sum_r A(m,r) * B(n,r), stored transposed: out[n*ldo + m]. The M role
+// is always given to the dimension that is contiguous in the OUTPUT, so that the 32 lanes of an
+// epilogue warp (= 32 consecutive TMEM lanes = 32 consecutive m) write 128 contiguous bytes.
+//   forward   Y[b][f]  : M=f (A = W  [f][k], K-major),  N=b (B = X  [b][k], K-major),  R=k
+//   dgrad     dX[b][k] : M=k (A = W  [f][k], MN-major), N=b (B = dZ [b][f], K-major),  R=f
+//   wgrad     dW[f][k] : M=k (A = X  [b][k], MN-major), N=f (B = dZ [b][f], MN-major), R=b
+//
+// One CTA computes one 128 x BN output tile for one K split. Warp roles: warp 0 = TMA producer,
+// warp 1 = TMEM allocator + single-thread MMA issuer, warps 2..5 = epilogue (TMEM lane quarters).
+#include "gemm.h"
+
+#include <cuda.h>
+#include <cudaTypedefs.h>
+
+#include <mutex>
+
+namespace b200 {
+
+namespace {
+
+constexpr int BM = 128;          // UMMA_M (cta_group::1)
+constexpr int BK = 32;           // fp32 elements per k-block = one 128-byte swizzle span
+constexpr int UMMA_K = 8;        // kind::tf32: 32 bytes of K per instruction
+constexpr int kThreads = 192;
+constexpr uint32_t kSpinLimit = 1u << 28;  // bounded waits: trap instead of hanging the GPU box
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  const uint32_t addr = smem_u32(bar);
+  uint32_t done = 0, spins = 0;
+  while (true) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(done)
+        : "r"(addr), "r"(parity)
+        : "memory");
+    if (done) break;
+    if (++spins > kSpinLimit) {
+      printf("b200ddp tf32 gemm: mbarrier wait timed out (block %d,%d,%d thread %d)\n", blockIdx.x, blockIdx.y,
+             blockIdx.z, threadIdx.x);
+      __trap();
+    }
+  }
+}
+__device__ __forceinline__ void tma_load_2d(void* smem_dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+      ::"r"(smem_u32(smem_dst)), "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_alloc(uint32_t* slot, uint32_t ncols) {
+  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(slot)), "r"(ncols) : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t ncols) {
+  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
+}
+__device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+
+// 32 lanes x 32 consecutive fp32 columns of TMEM -> 32 registers per thread.
+__device__ __forceinline__ void tmem_ld_32x32(uint32_t taddr, uint32_t (&r)[32]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,"
+      "%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+        "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
+        "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
+        "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr)
+      : "memory");
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+// Shared-memory matrix descriptor (sm_100 format, version 1), SWIZZLE_128B.
+//   K-major tile  [rows][32 fp32]: 8-row groups are 1024 B apart (SBO); LBO unused (1).
+//   MN-major tile: 32-element (128 B) MN atoms x 8 k-rows = 1024 B; next k-group +1024 B (SBO),
+//                  next MN atom +4096 B (LBO) because each TMA box is 32 k-rows x 128 B.
+__device__ __forceinline__ uint64_t make_smem_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+  const uint32_t lo = ((saddr & 0x3FFFFu) >> 4) | ((lbo_bytes >> 4) << 16);
+  const uint32_t hi = (sbo_bytes >> 4) | (1u << 14) /* version */ | (2u << 29) /* SWIZZLE_128B */;
+  return (uint64_t)lo | ((uint64_t)hi << 32);
+}
+
+struct KParams {
+  int M, N, R;
+  int kblocks_per_split;
+  int splits;
+  int stages;
+  int a_mn, b_mn;
+  float* out;
+  long long ldo;
+  float* ws;
+  Epilogue ep;
+};
+
+template <int BN>
+__global__ void __launch_bounds__(kThreads)
+tf32_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, KParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  // 1024-byte alignment is required by the 128B swizzle pattern (TMA and UMMA must agree on it).
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  constexpr uint32_t A_BYTES = BM * BK * 4;   // 16 KB
+  constexpr uint32_t B_BYTES = BN * BK * 4;
+  constexpr uint32_t STAGE_BYTES = A_BYTES + B_BYTES;
+  const int stages = p.stages;
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + (size_t)stages * STAGE_BYTES);
+  uint64_t* empty_bar = full_bar + stages;
+  uint64_t* tmem_full_bar = empty_bar + stages;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full_bar + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int m0 = blockIdx.x * BM, n0 = blockIdx.y * BN, z = blockIdx.z;
+  const int total_kb = (p.R + BK - 1) / BK;
+  const int kb_begin = z * p.kblocks_per_split;
+  int kb_end = kb_begin + p.kblocks_per_split;
+  if (kb_end > total_kb) kb_end = total_kb;
+  const int nkb = kb_end - kb_begin;   // host guarantees >= 1
+
+  if (warp == 0 && lane == 0) {
+    for (int s = 0; s < stages; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    mbar_init(tmem_full_bar, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmA) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmB) : "memory");
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, BN);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0 && lane == 0) {
+    // ---------------- TMA producer ----------------
+    for (int i = 0; i < nkb; ++i) {
+      const int s = i % stages;
+      const uint32_t ph = (uint32_t)(i / stages) & 1u;
+      mbar_wait(&empty_bar[s], ph ^ 1u);
+      mbar_arrive_expect_tx(&full_bar[s], STAGE_BYTES);
+      uint8_t* sa = smem + (size_t)s * STAGE_BYTES;
+      uint8_t* sb = sa + A_BYTES;
+      const int r0 = (kb_begin + i) * BK;
+      if (!p.a_mn) {
+        tma_load_2d(sa, &tmA, &full_bar[s], r0, m0);                       // box {32 r, 128 m}
+      } else {
+#pragma unroll
+        for (int j = 0; j < BM / 32; ++j) tma_load_2d(sa + j * 4096, &tmA, &full_bar[s], m0 + 32 * j, r0);  // box {32 m, 32 r}
+      }
+      if (!p.b_mn) {
+        tma_load_2d(sb, &tmB, &full_bar[s], r0, n0);                       // box {32 r, BN n}
+      } else {
+#pragma unroll
+        for (int j = 0; j < BN / 32; ++j) tma_load_2d(sb + j * 4096, &tmB, &full_bar[s], n0 + 32 * j, r0);
+      }
+    }
+  } else if (warp == 1 && lane == 0) {
+    // ---------------- MMA issuer (one thread) ----------------
+    const uint32_t idesc = (1u << 4)                      // D format  = F32
+                           | (2u << 7) | (2u << 10)       // A, B format = TF32
+                           | ((uint32_t)p.a_mn << 15) | ((uint32_t)p.b_mn << 16)
+                           | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+    const uint32_t a_lbo = p.a_mn ? 4096u : 16u, a_sbo = 1024u, a_adv = p.a_mn ? 1024u : (uint32_t)(UMMA_K * 4);
+    const uint32_t b_lbo = p.b_mn ? 4096u : 16u, b_sbo = 1024u, b_adv = p.b_mn ? 1024u : (uint32_t)(UMMA_K * 4);
+    for (int i = 0; i < nkb; ++i) {
+      const int s = i % stages;
+      const uint32_t ph = (uint32_t)(i / stages) & 1u;
+      mbar_wait(&full_bar[s], ph);
+      tc_fence_after();
+      const uint32_t sa = smem_u32(smem + (size_t)s * STAGE_BYTES);
+      const uint32_t sb = sa + A_BYTES;
+#pragma unroll
+      for (int k = 0; k < BK / UMMA_K; ++k) {
+        const uint64_t adesc = make_smem_desc(sa + k * a_adv, a_lbo, a_sbo);
+        const uint64_t bdesc = make_smem_desc(sb + k * b_adv, b_lbo, b_sbo);
+        umma_tf32(tmem_base, adesc, bdesc, idesc, (i > 0 || k > 0) ? 1u : 0u);
+      }
+      umma_commit(&empty_bar[s]);        // frees this smem stage when the MMAs above retire
+    }
+    umma_commit(tmem_full_bar);          // accumulator complete -> epilogue may read TMEM
+  } else if (warp >= 2) {
+    // ---------------- epilogue: TMEM -> registers -> global ----------------
+    mbar_wait(tmem_full_bar, 0);
+    tc_fence_after();
+    const int q = warp & 3;                              // TMEM lane quarter this warp may touch
+    const int m = m0 + q * 32 + lane;
+    const bool m_ok = m < p.M;
+    float* dst;
+    long long ld;
+    if (p.splits > 1) { dst = p.ws + (size_t)z * (size_t)p.N * (size_t)p.M; ld = p.M; }
+    else { dst = p.out; ld = p.ldo; }
+#pragma unroll 1
+    for (int c = 0; c < BN; c += 32) {
+      uint32_t r[32];
+      tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c, r);
+      if (m_ok) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+          const int n = n0 + c + j;
+          if (n < p.N) {
+            float v = __uint_as_float(r[j]);
+            if (p.splits == 1) v = apply_epilogue(v, p.ep, n, m, ld);
+            dst[(long long)n * ld + m] = v;
+          }
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem_base, BN);
+}
+
+// ------------------------------------------------------------------------------------------------
+// host side
+// ------------------------------------------------------------------------------------------------
+PFN_cuTensorMapEncodeTiled_v12000 g_encode = nullptr;
+std::once_flag g_encode_once;
+
+int get_encode() {
+  std::call_once(g_encode_once, [] {
+    void* fn = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres) == cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess)
+      g_encode = reinterpret_cast<PFN_cuTensorMapEncodeTiled_v12000>(fn);
+  });
+  if (!g_encode) {
+    set_error("cuTensorMapEncodeTiled driver entry point unavailable");
+    return kNotInitialised;
+  }
+  return 0;
+}
+
+// 2-D fp32 tensor map over a row-major [outer x inner] matrix with row stride ld (elements).
+int make_map(CUtensorMap* map, const float* base, long long inner, long long outer, long long ld, int box_inner,
+             int box_outer) {
+  cuuint64_t gdim[2] = {(cuuint64_t)inner, (cuuint64_t)outer};
+  cuuint64_t gstr[1] = {(cuuint64_t)ld * 4ull};
+  cuuint32_t box[2] = {(cuuint32_t)box_inner, (cuuint32_t)box_outer};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = g_encode(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(base), gdim, gstr, box, estr,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_error("cuTensorMapEncodeTiled failed (CUresult %d) inner=%lld outer=%lld ld=%lld box=%dx%d", (int)r, inner,
+              outer, ld, box_inner, box_outer);
+    return kDriverErrBase + (int)r;
+  }
+  return 0;
+}
+
+template <int BN>
+int launch_bn(const CUtensorMap& tmA, const CUtensorMap& tmB, const KParams& p, cudaStream_t stream) {
+  const size_t stage_bytes = (size_t)(BM + BN) * BK * 4;
+  const size_t smem = 1024 + (size_t)p.stages * stage_bytes + (2 * p.stages + 1) * 8 + 16;
+  static bool attr_set = false;   // per template instance; benign race (idempotent)
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(tf32_gemm_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    if (e != cudaSuccess) {
+      set_error("cudaFuncSetAttribute(tf32_gemm_kernel) -> %s", cudaGetErrorString(e));
+      return kCudaErrBase + (int)e;
+    }
+    attr_set = true;
+  }
+  dim3 grid((p.M + BM - 1) / BM, (p.N + BN - 1) / BN, p.splits);
+  tf32_gemm_kernel<BN><<<grid, kThreads, smem, stream>>>(tmA, tmB, p);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) {
+    set_error("tf32_gemm_kernel<%d> launch (grid %d,%d,%d smem %zu) -> %s", BN, grid.x, grid.y, grid.z, smem,
+              cudaGetErrorString(e));
+    return kCudaErrBase + (int)e;
+  }
+  count_launch();
+  return 0;
+}
+
+}  // namespace
+
+int tf32_gemm_launch(const float* A, long long lda, int a_mn, const float* B, long long ldb, int b_mn, int M, int N,
+                     int R, float* out, long long ldo, int splits, float* ws, const Epilogue& ep,
+                     cudaStream_t stream) {
+  int rc = get_encode();
+  if (rc) return rc;
+  if ((((uintptr_t)A | (uintptr_t)B) & 15) || (lda & 3) || (ldb & 3)) {
+    set_error("tf32 gemm: operands must be 16-byte aligned with leading dimensions multiple of 4 (lda=%lld ldb=%lld)",
+              lda, ldb);
+    return kInvalidArg;
+  }
+  const int BN = (N > 64) ? 128 : 64;
+  CUtensorMap tmA, tmB;
+  rc = a_mn ? make_map(&tmA, A, M, R, lda, 32, 32) : make_map(&tmA, A, R, M, lda, BK, BM);
+  if (rc) return rc;
+  rc = b_mn ? make_map(&tmB, B, N, R, ldb, 32, 32) : make_map(&tmB, B, R, N, ldb, BK, BN);
+  if (rc) return rc;
+  const int total_kb = (R + BK - 1) / BK;
+  if (splits < 1) splits = 1;
+  if (splits > total_kb) splits = total_kb;
+  KParams p;
+  p.M = M; p.N = N; p.R = R;
+  p.kblocks_per_split = (total_kb + splits - 1) / splits;
+  p.splits = (total_kb + p.kblocks_per_split - 1) / p.kblocks_per_split;   // no empty splits
+  const int max_stages = (BN == 128) ? 6 : 8;
+  p.stages = p.kblocks_per_split < max_stages ? p.kblocks_per_split : max_stages;
+  if (p.stages < 2) p.stages = 2;
+  p.a_mn = a_mn; p.b_mn = b_mn;
+  p.out = out; p.ldo = ldo; p.ws = ws; p.ep = ep;
+  if (p.splits > 1 && !ws) {
+    set_error("tf32 gemm: split-K needs a workspace");
+    return kInvalidArg;
+  }
+  return BN == 128 ? launch_bn<128>(tmA, tmB, p, stream) : launch_bn<64>(tmA, tmB, p, stream);
+}
+
+}  // namespace b200
