@@ -1,0 +1,266 @@
+"""Per-rank bodies for the multi-process tests (spawned with torch.multiprocessing; gloo on CPU, nccl on GPU)."""
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+for _p in (ROOT, os.path.join(ROOT, "tutorial-torch-distributed-data-parallel_b200")):
+    if _p not in sys.path:
+        sys.path.insert(0, _p)
+
+import warnings  # noqa: E402
+
+import torch  # noqa: E402
+import torch.distributed as dist  # noqa: E402
+from torch import nn  # noqa: E402
+
+warnings.filterwarnings("ignore", message=".*plumbing mode.*")
+
+
+def _init(rank, world, port, backend="gloo"):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    torch.set_num_threads(2)
+    if backend == "nccl":
+        torch.cuda.set_device(rank)
+    dist.init_process_group(backend, rank=rank, world_size=world)
+
+
+def _mlp(seed=0):
+    torch.manual_seed(seed)
+    return nn.Sequential(nn.Linear(12, 300), nn.ReLU(), nn.Linear(300, 300), nn.ReLU(), nn.Linear(300, 5))
+
+
+def _data(rank, step, n=6):
+    g = torch.Generator().manual_seed(1000 + 17 * rank + step)
+    return torch.randn(n, 12, generator=g), torch.randint(0, 5, (n,), generator=g)
+
+
+def _gather_params(model, world):
+    flat = torch.cat([p.detach().reshape(-1).cpu() for p in model.parameters()])
+    out = [torch.empty_like(flat) for _ in range(world)]
+    dist.all_gather(out, flat)
+    return out
+
+
+def run(rank, world, port, case, out_dir, backend="gloo"):
+    _init(rank, world, port, backend)
+    try:
+        globals()["case_" + case](rank, world, out_dir, torch.device("cuda", rank) if backend == "nccl" else torch.device("cpu"))
+        dist.barrier()
+        if rank == 0:
+            open(os.path.join(out_dir, case + ".ok"), "w").write("ok")
+    finally:
+        dist.destroy_process_group()
+
+
+# ---- cases -----------------------------------------------------------------------------------------------------
+def case_mean_gradient(rank, world, out_dir, dev):
+    import b200ddp
+    twin = _mlp().to(dev)
+    model = _mlp(seed=rank + 5).to(dev)                 # different init per rank: ctor must broadcast rank 0's
+    ddp = b200ddp.DistributedDataParallel(model)
+    ref0 = _mlp(seed=5).to(dev)
+    for p, q in zip(model.parameters(), ref0.parameters()):
+        assert torch.equal(p.detach().cpu(), q.detach().cpu()), "parameters were not broadcast from rank 0"
+    twin.load_state_dict(model.state_dict())
+    x, y = _data(rank, 0)
+    x, y = x.to(dev), y.to(dev)
+    nn.functional.cross_entropy(twin(x), y).backward()
+    nn.functional.cross_entropy(ddp(x), y).backward()
+    for p, q in zip(model.parameters(), twin.parameters()):
+        local = q.grad.detach().cpu().clone()
+        dist.all_reduce(local)
+        assert torch.allclose(p.grad.cpu(), local / world, rtol=1e-5, atol=1e-7)
+        assert ddp.arena.grad_in_arena(ddp.arena.index_of(p))
+    # evaluation under no_grad must not arm the reducer
+    with torch.no_grad():
+        ddp.eval()
+        ddp(x)
+        ddp.train()
+
+
+def _stock_vs_ours(rank, world, dev, steps, ours_kwargs, stock_step):
+    import b200ddp
+    from torch.nn.parallel import DistributedDataParallel as TorchDDP
+    a = _mlp().to(dev)
+    b = _mlp().to(dev)
+    ours = b200ddp.DistributedDataParallel(a, **ours_kwargs)
+    stock = TorchDDP(b, device_ids=[dev.index] if dev.type == "cuda" else None)
+    opt_a = b200ddp.optim.Adam(ours.parameters(), lr=1e-3)
+    opt_b = torch.optim.Adam(stock.parameters(), lr=1e-3)
+    for s in range(steps):
+        x, y = _data(rank, s)
+        x, y = x.to(dev), y.to(dev)
+        opt_a.zero_grad()
+        la = nn.functional.cross_entropy(ours(x), y)
+        la.backward()
+        opt_a.step()
+        opt_b.zero_grad()
+        stock_step(stock, x, y, rank, s)
+        opt_b.step()
+        for p, q in zip(a.parameters(), b.parameters()):
+            assert torch.allclose(p.grad, q.grad, rtol=2e-5, atol=1e-7), f"grad mismatch at step {s}"
+            assert torch.allclose(p, q, rtol=1e-5, atol=1e-6), f"param mismatch at step {s}"
+    ps = _gather_params(a, world)
+    assert all(torch.equal(ps[0], t) for t in ps), "ranks diverged"
+    return ours, stock
+
+
+def case_parity_with_stock_ddp(rank, world, out_dir, dev):
+    def step(stock, x, y, rank, s):
+        nn.functional.cross_entropy(stock(x), y).backward()
+    ours, _ = _stock_vs_ours(rank, world, dev, 5, {}, step)
+    assert ours.reducer.first_ready_order is not None
+
+
+def _clip_restatement(kind, c):
+    """stock DDP under no_sync + local clip + manual all-reduce + divide."""
+    def step(stock, x, y, rank, s):
+        with stock.no_sync():
+            nn.functional.cross_entropy(stock(x), y).backward()
+        params = [p for p in stock.parameters()]
+        if kind == "norm":
+            torch.nn.utils.clip_grad_norm_(params, c)
+        else:
+            torch.nn.utils.clip_grad_value_(params, c)
+        for p in params:
+            dist.all_reduce(p.grad)
+            p.grad /= dist.get_world_size()
+    return step
+
+
+def case_clip_value_before_aggregation(rank, world, out_dir, dev):
+    _stock_vs_ours(rank, world, dev, 3, {"clip_grad_value": 0.01}, _clip_restatement("value", 0.01))
+
+
+def case_clip_norm_before_aggregation(rank, world, out_dir, dev):
+    ours, _ = _stock_vs_ours(rank, world, dev, 3, {"clip_grad_norm": 0.05}, _clip_restatement("norm", 0.05))
+    assert float(ours.reducer.last_local_norm) > 0.05      # the clip was active
+
+
+def case_no_sync_accumulation(rank, world, out_dir, dev):
+    import b200ddp
+    from torch.nn.parallel import DistributedDataParallel as TorchDDP
+    a, b = _mlp().to(dev), _mlp().to(dev)
+    ours = b200ddp.DistributedDataParallel(a)
+    stock = TorchDDP(b, device_ids=[dev.index] if dev.type == "cuda" else None)
+    for model in (ours, stock):
+        x0, y0 = _data(rank, 0)
+        x1, y1 = _data(rank, 1)
+        with model.no_sync():
+            nn.functional.cross_entropy(model(x0.to(dev)), y0.to(dev)).backward()
+        if model is ours:
+            local_only = [p.grad.detach().cpu().clone() for p in a.parameters()]
+        nn.functional.cross_entropy(model(x1.to(dev)), y1.to(dev)).backward()
+    for p, q in zip(a.parameters(), b.parameters()):
+        assert torch.allclose(p.grad, q.grad, rtol=2e-5, atol=1e-7)
+    # inside no_sync nothing was communicated: ranks held different gradients
+    flat = torch.cat([g.reshape(-1) for g in local_only])
+    out = [torch.empty_like(flat) for _ in range(world)]
+    dist.all_gather(out, flat)
+    assert not torch.equal(out[0], out[1])
+
+
+def case_fault_containment(rank, world, out_dir, dev):
+    """README.md:92-95: one rank's bad gradient must not wreck the aggregate when clipping comes first."""
+    import b200ddp
+    x, y = _data(rank, 0)
+    x, y = x.to(dev), y.to(dev)
+    # (a) huge but finite gradient on rank 1, norm clipping
+    m = _mlp().to(dev)
+    ddp = b200ddp.DistributedDataParallel(m, clip_grad_norm=1.0)
+    scale = 1e20 if rank == 1 else 1.0
+    (nn.functional.cross_entropy(ddp(x), y) * scale).backward()
+    total = torch.sqrt(sum((p.grad.double() ** 2).sum() for p in m.parameters()))
+    assert torch.isfinite(total) and float(total) <= 1.0 + 1e-4
+    # (b) NaN gradient on rank 1: stock semantics poison everybody, nonfinite='zero' contains it
+    m2 = _mlp().to(dev)
+    ddp2 = b200ddp.DistributedDataParallel(m2, clip_grad_norm=1.0, nonfinite="zero")
+    loss = nn.functional.cross_entropy(ddp2(x), y)
+    if rank == 1:
+        loss = loss * float("nan")
+    loss.backward()
+    assert all(torch.isfinite(p.grad).all() for p in m2.parameters())
+    assert any(float(p.grad.abs().sum()) > 0 for p in m2.parameters())
+    m3 = _mlp().to(dev)
+    ddp3 = b200ddp.DistributedDataParallel(m3, clip_grad_norm=1.0)
+    loss = nn.functional.cross_entropy(ddp3(x), y)
+    if rank == 1:
+        loss = loss * float("nan")
+    loss.backward()
+    assert not all(torch.isfinite(p.grad).all() for p in m3.parameters())   # README's warning, reproduced
+
+
+def case_checkpoint_rank0(rank, world, out_dir, dev):
+    import b200ddp
+    m = _mlp(seed=3).to(dev)
+    ddp = b200ddp.DistributedDataParallel(m)
+    path = os.path.join(out_dir, "ckpt_0.pt")
+    if rank == 0:                                    # reference :217-221
+        torch.save(ddp.state_dict(), path)
+    dist.barrier()                                   # reference :223
+    sd = torch.load(path, map_location="cpu")        # README.md:51-52
+    assert all(k.startswith("module.") for k in sd) and len(sd) == 6
+    fresh = b200ddp.DistributedDataParallel(_mlp(seed=9).to(dev))
+    fresh.load_state_dict(sd)
+    for (k, v), (_, w) in zip(fresh.state_dict().items(), ddp.state_dict().items()):
+        assert torch.equal(v.cpu(), w.cpu()), k
+
+
+def case_plumbing_alexnet(rank, world, out_dir, dev):
+    """BASELINE config 1: the toy model through our surface on CPU/gloo (host logic only)."""
+    import b200ddp
+    from oracle import reference_loop as rl
+    x, y = rl.synthetic_pool(32, seed=1, hw=224)
+    ds = torch.utils.data.TensorDataset(x, y)
+    sampler = b200ddp.DistributedSampler(ds, shuffle=True, num_replicas=world, rank=rank)
+    loader = torch.utils.data.DataLoader(ds, batch_size=8, sampler=sampler)
+    model = rl.make_model(seed=0)
+    ddp = b200ddp.DistributedDataParallel(model)
+    opt = b200ddp.optim.Adam(ddp.parameters(), lr=0.001)
+    sampler.set_epoch(0)
+    seen = []
+    losses = []
+    rl.train_epoch(ddp, loader, nn.CrossEntropyLoss(), opt, torch.device("cpu"), max_steps=2, losses=losses)
+    seen = list(sampler)
+    allseen = [None] * world
+    dist.all_gather_object(allseen, seen)
+    assert not set(allseen[0]) & set(allseen[1])               # disjoint shards
+    ps = _gather_params(model, world)
+    assert torch.equal(ps[0], ps[1])                           # replicas stay identical
+    assert ddp.bucket_sizes() == [67289128, 151011328, 9878784]
+    if rank == 0:
+        torch.save(ddp.state_dict(), os.path.join(out_dir, "ckpt_0.pt"))
+    dist.barrier()
+    sd = torch.load(os.path.join(out_dir, "ckpt_0.pt"), map_location="cpu")
+    assert len(sd) == 16 and list(sd)[0] == "module.features.0.weight"
+
+
+def case_accelerator(rank, world, out_dir, dev):
+    import b200ddp
+    from b200ddp.accelerate import Accelerator
+    os.environ.update(RANK=str(rank), WORLD_SIZE=str(world), LOCAL_RANK=str(rank))
+    acc = Accelerator(cpu=(dev.type == "cpu"))
+    assert acc.num_processes == world and acc.is_local_main_process == (rank == 0)
+    model = _mlp().to(acc.device)
+    opt = b200ddp.optim.Adam(model.parameters(), lr=1e-3)
+    g = torch.Generator().manual_seed(0)
+    ds = torch.utils.data.TensorDataset(torch.randn(44, 12, generator=g), torch.randint(0, 5, (44,), generator=g))
+    loader = torch.utils.data.DataLoader(ds, batch_size=4)
+    model, opt, loader = acc.prepare(model, opt, loader)
+    assert isinstance(model, b200ddp.DistributedDataParallel)
+    n = 0
+    for xb, yb in loader:
+        assert xb.device.type == acc.device.type and xb.shape[0] == 4
+        opt.zero_grad()
+        loss = nn.functional.cross_entropy(model(xb), yb)
+        acc.backward(loss)
+        opt.step()
+        n += 1
+    assert n == len(loader) == 6                     # 11 batches over 2 ranks, evened out
+    ps = _gather_params(model.module, world)
+    assert torch.equal(ps[0], ps[1])
+    acc.wait_for_everyone()
+    acc.save_model(model, os.path.join(out_dir, "acc"))
+    acc.wait_for_everyone()
+    assert os.path.exists(os.path.join(out_dir, "acc", "model.safetensors"))
