@@ -1,0 +1,379 @@
+#!/usr/bin/env python
+"""bench.py — train samples/sec of the DDP training step of the toy model (BASELINE.json metric).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+
+Workload (BASELINE.json configs[1] at N=1, configs[2] for N>1): torchvision-AlexNet-10 (hidden 4096,
+57,044,810 fp32 parameters), per-rank batch 128 of synthetic [3,224,224] fp32 images, CrossEntropy,
+Adam(lr 1e-3), dropout 0.5 on — one "step" = zero_grad, forward, loss, backward (bucketed gradient
+all-reduce when N>1), optimizer step: reference multi-GPU-training-torch.py:118-126.
+
+Own arm: one process per GPU (torchrun env for N>1), timing with CUDA events on the compute stream
+bracketed by barrier + synchronize, max over ranks. `value` has the inputs resident in HBM (batches are
+gathered from a 1024-sample device pool through DistributedSampler indices); `e2e` copies every step's
+batch from pinned host memory and reads every step's loss back. The working set of a step (77 MB batch
++ 228 MB weights + 228 MB gradients + 456 MB Adam moments) is several times the 126 MB L2.
+
+Reference arm (`--impl reference`): the reference's CPU path (oracle/reference_loop.py: stock torch +
+torchvision on the host cores, the restatement checked against the reference's own train()).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for _p in (ROOT, os.path.join(ROOT, "tutorial-torch-distributed-data-parallel_b200")):
+    if _p not in sys.path:
+        sys.path.insert(0, _p)
+
+BATCH = 128
+POOL = 1024
+VIRTUAL_N = 50_000
+P_PARAMS = 57_044_810
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=30)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--mode", default="tf32", choices=["tf32", "fp32"])
+    ap.add_argument("--hidden", type=int, default=4096)
+    ap.add_argument("--batch", type=int, default=BATCH)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+# ---- clocks ---------------------------------------------------------------------------------------------------
+class ClockSampler:
+    QUERY = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+             "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+             "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int) -> None:
+        self.index = index
+        self.proc = None
+        self.lines = []
+
+    def start(self) -> None:
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.QUERY}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self) -> None:
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self) -> dict:
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [c.strip() for c in ln.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0]))
+                mx.append(float(f[1]))
+            except ValueError:
+                continue
+            for n, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ---- reference arm ----------------------------------------------------------------------------------------------
+def run_reference(args) -> None:
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import torch
+    from oracle import reference_loop as rl
+    cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+    torch.set_num_threads(cores)
+    model = rl.make_model(seed=1234, hidden=args.hidden)
+    crit = torch.nn.CrossEntropyLoss()
+    opt = torch.optim.Adam(model.parameters(), lr=0.001)
+    dev = torch.device("cpu")
+    batch = args.batch
+    x, y = rl.synthetic_pool(batch, seed=7)
+    t0 = time.perf_counter()
+    rl.train_epoch(model, [(x, y)], crit, opt, dev)          # first (cold) step, also sizes the sample
+    first = time.perf_counter() - t0
+    budget = 240.0
+    if first * (args.steps + args.warmup) > budget and batch > 16:
+        batch = max(16, int(batch * budget / (first * (args.steps + args.warmup))) // 16 * 16)
+        x, y = x[:batch], y[:batch]
+    for _ in range(max(args.warmup - 1, 0)):
+        rl.train_epoch(model, [(x, y)], crit, opt, dev)
+    times = []
+    for _ in range(args.steps):
+        t0 = time.perf_counter()
+        rl.train_epoch(model, [(x, y)], crit, opt, dev)
+        times.append(time.perf_counter() - t0)
+    total = sum(times)
+    value = batch * args.steps / total
+    sample = (f"{args.steps} timed CPU training steps of batch {batch} (per-rank batch of the workload is {args.batch}); "
+              f"stock torch {torch.__version__} + torchvision AlexNet-10 + Adam on {cores} host threads, ws=1")
+    line = {"impl": "reference", "metric": "train_samples_per_sec", "value": value, "unit": "samples/s",
+            "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * total / args.steps,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "fp32", "data": "synthetic",
+            "config": workload_config(args, batch_override=batch),
+            "cpu_baseline": {"value": value, "unit": "samples/s", "cores": cores, "kind": "port", "sample": sample},
+            "e2e": {"value": value, "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+def workload_config(args, batch_override=None) -> dict:
+    return {"workload": "AlexNet-10 DDP training step (BASELINE.json configs[1]; configs[2] when n_gpus>1): "
+                        "zero_grad + forward + CrossEntropy + backward + bucketed grad all-reduce + Adam",
+            "per_rank_batch": batch_override or args.batch, "global_batch": (batch_override or args.batch) * args.gpus,
+            "input": "[3,224,224] fp32 synthetic", "hidden": args.hidden, "params": P_PARAMS if args.hidden == 4096 else None,
+            "optimizer": "Adam lr=1e-3", "dropout": 0.5, "parallelism": f"dp{args.gpus}",
+            "l2": "working set per step (77 MB batch + 912 MB weights/grads/moments) >> 126 MB L2; inputs rotate "
+                  "through a 1024-sample pool"}
+
+
+# ---- own arm ------------------------------------------------------------------------------------------------------
+def run_b200(args) -> None:
+    import torch
+    import torch.distributed as dist
+
+    import b200ddp
+    from b200ddp import _lib
+    from b200ddp.models import AlexNet
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus:
+        if world == 1 and args.gpus > 1:
+            raise SystemExit("--gpus N>1 must be launched with torch.distributed.run --nproc-per-node N")
+    assert torch.cuda.is_available(), "bench.py (own arm) needs a GPU: there is no CPU fallback"
+    dev = torch.device("cuda", local)
+    torch.cuda.set_device(dev)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    _lib.load()
+
+    B = args.batch
+    torch.manual_seed(1234)
+    model = AlexNet(hidden=args.hidden, dropout=0.5, mode=args.mode).to(dev)
+    ddp = b200ddp.DistributedDataParallel(model, device_ids=[local])
+    opt = b200ddp.optim.Adam(ddp.parameters(), lr=0.001)
+    crit = b200ddp.CrossEntropyLoss()
+    ddp.train()
+
+    # synthetic pool resident in HBM + sampler-driven batch indices (S1 stays on the path)
+    gcpu = torch.Generator().manual_seed(7)
+    pool_y_cpu = torch.randint(0, 10, (POOL,), generator=gcpu)
+    gdev = torch.Generator(device=dev).manual_seed(7)
+    pool_x = torch.randn(POOL, 3, 224, 224, device=dev, generator=gdev)
+    pool_y = pool_y_cpu.to(dev)
+
+    class _Virtual:
+        def __len__(self):
+            return VIRTUAL_N
+    sampler = b200ddp.DistributedSampler(_Virtual(), num_replicas=world, rank=rank, shuffle=True)
+    total_steps = args.steps + args.warmup
+    idx = []
+    epoch = 0
+    while len(idx) < total_steps * B * 2 + B:
+        sampler.set_epoch(epoch)
+        idx += list(sampler)
+        epoch += 1
+    idx_dev = (torch.tensor(idx, dtype=torch.int64) % POOL).to(dev)
+
+    def step_resident(i):
+        sel = idx_dev[i * B:(i + 1) * B]
+        x = pool_x.index_select(0, sel)
+        y = pool_y.index_select(0, sel)
+        opt.zero_grad()
+        loss = crit(ddp(x), y)
+        loss.backward()
+        opt.step()
+        return loss
+
+    def sync_all():
+        torch.cuda.synchronize(dev)
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize(dev)
+
+    # ---- warm-up -----------------------------------------------------------------------------------------------
+    for i in range(args.warmup):
+        step_resident(i)
+    sync_all()
+
+    # ---- timed region: device-resident inputs ------------------------------------------------------------------------
+    clocks = ClockSampler(local)
+    if rank == 0:
+        clocks.start()
+        time.sleep(0.15)
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    adam_ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    launches0 = _lib.launch_count()
+    sync_all()
+    ev0.record()
+    for k in range(args.steps):
+        i = args.warmup + k
+        sel = idx_dev[i * B:(i + 1) * B]
+        x = pool_x.index_select(0, sel)
+        y = pool_y.index_select(0, sel)
+        opt.zero_grad()
+        loss = crit(ddp(x), y)
+        loss.backward()
+        adam_ev[k][0].record()
+        opt.step()
+        adam_ev[k][1].record()
+    ev1.record()
+    sync_all()
+    launches = _lib.launch_count() - launches0
+    ms = ev0.elapsed_time(ev1)
+    final_loss = float(loss)
+    adam_ms = [a.elapsed_time(b) for a, b in adam_ev]
+    clock_info = clocks.stop() if rank == 0 else None
+    t = torch.tensor([ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_max = float(t)
+
+    # ---- timed region: end to end (pinned host batches -> device, loss read back every step) -----------------------------
+    ring = 4
+    host_x = [torch.randn(B, 3, 224, 224, generator=gcpu).pin_memory() for _ in range(ring)]
+    host_y = [torch.randint(0, 10, (B,), generator=gcpu).pin_memory() for _ in range(ring)]
+    dev_x = [torch.empty(B, 3, 224, 224, device=dev) for _ in range(2)]
+    dev_y = [torch.empty(B, dtype=torch.int64, device=dev) for _ in range(2)]
+    loss_host = torch.zeros(args.steps + 2, dtype=torch.float32).pin_memory()
+    copy_stream = torch.cuda.Stream(dev)
+    ready = [torch.cuda.Event() for _ in range(2)]
+    consumed = [torch.cuda.Event() for _ in range(2)]
+    main = torch.cuda.current_stream(dev)
+
+    def prefetch(j):
+        slot = j % 2
+        with torch.cuda.stream(copy_stream):
+            copy_stream.wait_event(consumed[slot])
+            dev_x[slot].copy_(host_x[j % ring], non_blocking=True)
+            dev_y[slot].copy_(host_y[j % ring], non_blocking=True)
+            ready[slot].record(copy_stream)
+
+    def e2e_steps(n, record_from=0):
+        for s in range(2):
+            consumed[s].record(main)
+        prefetch(0)
+        for j in range(n):
+            slot = j % 2
+            if j + 1 < n:
+                prefetch(j + 1)
+            main.wait_event(ready[slot])
+            opt.zero_grad()
+            loss = crit(ddp(dev_x[slot]), dev_y[slot])
+            loss.backward()
+            opt.step()
+            consumed[slot].record(main)
+            loss_host[record_from + j].copy_(loss.detach(), non_blocking=True)   # D2H of this step's loss
+        main.synchronize()
+
+    e2e_steps(2)                       # warm the path (pinned buffers, copy stream)
+    sync_all()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t_wall0 = time.perf_counter()
+    e0.record()
+    e2e_steps(args.steps, record_from=2)
+    e1.record()
+    sync_all()
+    e2e_wall = time.perf_counter() - t_wall0
+    e2e_ms = e0.elapsed_time(e1)
+    te = torch.tensor([e2e_ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(te, op=dist.ReduceOp.MAX)
+    e2e_ms_max = float(te)
+    h2d = B * 3 * 224 * 224 * 4 + B * 8
+    d2h = 4
+
+    if rank == 0:
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except Exception:
+            pass
+        hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
+        peak_src = "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else "fallback 6650 GB/s"
+        n_arena = ddp.arena.numel
+        adam_t = statistics.mean(adam_ms) * 1e-3
+        adam_bytes = 28.0 * n_arena
+        achieved = adam_bytes / adam_t / 1e9
+        value = world * B * args.steps / (ms_max * 1e-3)
+        line = {
+            "metric": "train_samples_per_sec", "value": value, "unit": "samples/s", "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_max / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None,
+            "dtype": "tf32" if args.mode == "tf32" else "fp32", "data": "synthetic",
+            "config": workload_config(args),
+            "clocks": clock_info,
+            "e2e": {"value": world * B * args.steps / (e2e_ms_max * 1e-3), "unit": "samples/s",
+                    "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "ms_per_step": e2e_ms_max / args.steps,
+                    "wall_ms_per_step": 1e3 * e2e_wall / args.steps},
+            "gpu_launches": int(launches),
+            "roofline": {"kernel": "adam_flat_kernel (O1: single-pass Adam over the flat arenas)", "bound": "hbm",
+                         "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,
+                         "traffic": None, "algorithmic_bytes_per_launch": adam_bytes,
+                         "avg_launch_ms": adam_t * 1e3, "peak_source": peak_src,
+                         "share_of_step": adam_t * 1e3 / (ms_max / args.steps)},
+            "final_loss": final_loss,
+            "nccl": None,
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            try:
+                from oracle import reference_loop as rl
+                cb = rl.time_cpu_train(batch=B, steps=3, warmup=1, hidden=args.hidden)
+                line["cpu_baseline"] = {"value": cb["samples_per_s"], "unit": "samples/s", "cores": cb["cores"],
+                                        "kind": "port",
+                                        "sample": f"3 timed + 1 warm-up CPU training steps of batch {B} "
+                                                  f"(stock torch/torchvision AlexNet-10 + Adam, ws=1, {cb['cores']} threads); "
+                                                  f"median {cb['ms_per_step']:.0f} ms/step"}
+            except Exception as e:  # pragma: no cover
+                line["cpu_baseline"] = {"value": None, "unit": "samples/s", "cores": None, "kind": "port",
+                                        "sample": f"failed: {e}"}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        from b200ddp import comm as _comm
+        _comm.destroy_all()
+        dist.destroy_process_group()
+
+
+def main() -> None:
+    args = parse()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_b200(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -264,3 +264,66 @@ def case_accelerator(rank, world, out_dir, dev):
     acc.save_model(model, os.path.join(out_dir, "acc"))
     acc.wait_for_everyone()
     assert os.path.exists(os.path.join(out_dir, "acc", "model.safetensors"))
+
+
+def case_alexnet_vs_stock_ddp(rank, world, out_dir, dev):
+    """BASELINE config 3: toy model, DistributedSampler + set_epoch, our DDP/Adam/CE vs the stock stack."""
+    import b200ddp
+    from b200ddp.models import AlexNet
+    from oracle import reference_loop as rl
+    from torch.nn.parallel import DistributedDataParallel as TorchDDP
+    torch.backends.cudnn.allow_tf32 = False
+    tv = rl.make_model(seed=1234, dropout=0.0).to(dev)
+    ours = AlexNet(dropout=0.0, mode="fp32")
+    ours.load_state_dict(tv.state_dict())
+    ours = ours.to(dev)
+    ddp = b200ddp.DistributedDataParallel(ours, device_ids=[rank])
+    stock = TorchDDP(tv, device_ids=[rank])
+    opt = b200ddp.optim.Adam(ddp.parameters(), lr=1e-4)
+    opt_ref = torch.optim.Adam(stock.parameters(), lr=1e-4)
+    x, y = rl.synthetic_pool(96, seed=7)
+    ds = torch.utils.data.TensorDataset(x, y)
+    sa = b200ddp.DistributedSampler(ds, shuffle=True, num_replicas=world, rank=rank)
+    sb = torch.utils.data.DistributedSampler(ds, shuffle=True, num_replicas=world, rank=rank)
+    for epoch in (0, 1):
+        sa.set_epoch(epoch)
+        sb.set_epoch(epoch)
+        assert list(sa) == list(sb)
+        la, lb = [], []
+        rl.train_epoch(ddp, torch.utils.data.DataLoader(ds, batch_size=16, sampler=sa), b200ddp.CrossEntropyLoss(),
+                       opt, dev, losses=la)
+        rl.train_epoch(stock, torch.utils.data.DataLoader(ds, batch_size=16, sampler=sb), nn.CrossEntropyLoss(),
+                       opt_ref, dev, losses=lb)
+        for a, b in zip(la, lb):
+            assert abs(a - b) < 5e-4 * abs(b), (la, lb)
+    for (k, p), (_, q) in zip(ours.named_parameters(), tv.named_parameters()):
+        rel = float((p.detach().double() - q.detach().double()).norm() / q.detach().double().norm())
+        assert rel < 5e-4, (k, rel)
+    ps = _gather_params(ours, world)
+    assert all(torch.equal(ps[0], t) for t in ps)
+    assert ddp.bucket_sizes() == [67289128, 151011328, 9878784]
+
+
+def case_syncbn_two_ranks(rank, world, out_dir, dev):
+    """BASELINE config 4 (scaled down): convert_sync_batchnorm + DDP vs plain BN on the global batch."""
+    import b200ddp
+    torch.manual_seed(0)
+    C = 64
+    net = nn.Sequential(nn.Conv2d(3, C, 3, padding=1), nn.BatchNorm2d(C), nn.ReLU(), nn.Conv2d(C, 8, 3, padding=1))
+    ref = nn.Sequential(nn.Conv2d(3, C, 3, padding=1), nn.BatchNorm2d(C), nn.ReLU(), nn.Conv2d(C, 8, 3, padding=1))
+    ref.load_state_dict(net.state_dict())
+    net = b200ddp.SyncBatchNorm.convert_sync_batchnorm(net).to(dev)       # README.md:79-81: convert, then wrap
+    ddp = b200ddp.DistributedDataParallel(net, device_ids=[rank])
+    ref = ref.to(dev)
+    g = torch.Generator().manual_seed(5)
+    xall = torch.randn(world * 6, 3, 20, 20, generator=g).to(dev)
+    xloc = xall[rank * 6:(rank + 1) * 6]
+    out = ddp(xloc)
+    out.square().mean().backward()
+    oref = ref(xall)
+    (oref.square().mean()).backward()        # mean over the global batch == mean over ranks of local means
+    assert torch.allclose(out, oref[rank * 6:(rank + 1) * 6], rtol=1e-3, atol=1e-4)
+    assert torch.allclose(net[1].running_mean, ref[1].running_mean, rtol=1e-4, atol=1e-6)
+    assert torch.allclose(net[1].running_var, ref[1].running_var, rtol=1e-4, atol=1e-6)
+    for (k, p), (_, q) in zip(net.named_parameters(), ref.named_parameters()):
+        assert torch.allclose(p.grad, q.grad, rtol=2e-3, atol=1e-5), k

@@ -85,14 +85,17 @@ sqnorm_kernel(const float* __restrict__ g, long long n, double* __restrict__ par
   __shared__ double red[32];
   __shared__ bool last;
   const long long n4 = n >> 2, stride = (long long)gridDim.x * blockDim.x;
-  float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+  // fp64 accumulation: the pass is HBM-bound, and squares of large (but finite) gradients must not
+  // overflow before the clip coefficient can tame them
+  double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += stride) {
     const float4 v = ld_stream(reinterpret_cast<const float4*>(g) + i);
-    a0 = fmaf(v.x, v.x, a0); a1 = fmaf(v.y, v.y, a1); a2 = fmaf(v.z, v.z, a2); a3 = fmaf(v.w, v.w, a3);
+    a0 = fma((double)v.x, (double)v.x, a0); a1 = fma((double)v.y, (double)v.y, a1);
+    a2 = fma((double)v.z, (double)v.z, a2); a3 = fma((double)v.w, (double)v.w, a3);
   }
   const long long t = (n4 << 2) + (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (t < n) a0 = fmaf(g[t], g[t], a0);
-  double acc = (double)a0 + (double)a1 + (double)a2 + (double)a3;
+  if (t < n) a0 = fma((double)g[t], (double)g[t], a0);
+  double acc = a0 + a1 + a2 + a3;
   acc = block_sum<double>(acc, red);
   if (threadIdx.x == 0) {
     partials[blockIdx.x] = acc;
