@@ -28,7 +28,11 @@ static inline int bn_splits(int B, int C) {
   return s < 1 ? 1 : s;
 }
 
-static inline long long bn_ticket_bytes(int C) { return (((long long)C * 4 + 255) / 256) * 256; }
+// Scratch layout: [tickets: kBnMaxChannels x u32][partials]. The ticket region has a FIXED size so that a
+// scratch buffer shared by layers with different channel counts never sees one layer's partial sums where
+// another layer expects zeroed tickets (tickets are reset to zero by the kernel that used them).
+constexpr int kBnMaxChannels = 4096;
+static inline long long bn_ticket_bytes(int) { return (long long)kBnMaxChannels * 4; }
 
 __global__ void __launch_bounds__(kBnThreads)
 bn_stats_kernel(const float* __restrict__ x, int B, int C, int HW, float eps, double* __restrict__ partials,
@@ -198,6 +202,7 @@ long long b200ddp_bn_scratch_bytes(int B, int C) {
 int b200ddp_bn_stats(const float* x, int B, int C, int HW, float eps, float* mean, float* invstd, void* scratch,
                      long long scratch_bytes, int device, void* stream) {
   B200_CHECK_ARG(x && mean && invstd && scratch && B > 0 && C > 0 && HW > 0, "bn_stats: bad argument");
+  B200_CHECK_ARG(C <= kBnMaxChannels, "bn_stats: at most %d channels", kBnMaxChannels);
   B200_CHECK_ARG(scratch_bytes >= b200ddp_bn_scratch_bytes(B, C), "bn_stats: scratch too small");
   B200_CHECK_ARG(((uintptr_t)scratch & 255) == 0, "bn_stats: scratch must be 256-byte aligned");
   B200_DEVICE(device);
@@ -235,6 +240,7 @@ int b200ddp_bn_bwd_reduce(const float* dy, const float* x, const float* y_relu, 
                           void* scratch, long long scratch_bytes, int device, void* stream) {
   B200_CHECK_ARG(dy && x && mean && invstd && sum_dy && sum_dy_xmu && scratch && B > 0 && C > 0 && HW > 0,
                  "bn_bwd_reduce: bad argument");
+  B200_CHECK_ARG(C <= kBnMaxChannels, "bn_bwd_reduce: at most %d channels", kBnMaxChannels);
   B200_CHECK_ARG(scratch_bytes >= b200ddp_bn_scratch_bytes(B, C), "bn_bwd_reduce: scratch too small");
   B200_CHECK_ARG(((uintptr_t)scratch & 255) == 0, "bn_bwd_reduce: scratch must be 256-byte aligned");
   B200_DEVICE(device);

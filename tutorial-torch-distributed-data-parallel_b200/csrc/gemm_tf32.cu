@@ -102,13 +102,17 @@ __device__ __forceinline__ void tmem_ld_32x32(uint32_t taddr, uint32_t (&r)[32])
   asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
 
-// Shared-memory matrix descriptor (sm_100 format, version 1), SWIZZLE_128B.
-//   K-major tile  [rows][32 fp32]: 8-row groups are 1024 B apart (SBO); LBO unused (1).
-//   MN-major tile: 32-element (128 B) MN atoms x 8 k-rows = 1024 B; next k-group +1024 B (SBO),
-//                  next MN atom +4096 B (LBO) because each TMA box is 32 k-rows x 128 B.
-__device__ __forceinline__ uint64_t make_smem_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+// Shared-memory matrix descriptor (sm_100 format, version 1).
+//   K-major tile  [rows][32 fp32], SWIZZLE_128B (layout type 2): 8-row groups are 1024 B apart (SBO);
+//                  LBO unused (1).
+//   MN-major tile, 32-bit operands: the only legal layout is SWIZZLE_128B_BASE32B (layout type 1; TMA
+//                  swizzle 128B_ATOM_32B): rows of 32 MN-contiguous elements (128 B) whose 32-byte chunks
+//                  are XOR-ed with (row % 4); a k-group is 4 rows = 512 B (SBO); the next 32-element MN
+//                  atom is +4096 B (LBO) because each TMA box holds 32 k-rows x 128 B.
+__device__ __forceinline__ uint64_t make_smem_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes,
+                                                   uint32_t layout_type) {
   const uint32_t lo = ((saddr & 0x3FFFFu) >> 4) | ((lbo_bytes >> 4) << 16);
-  const uint32_t hi = (sbo_bytes >> 4) | (1u << 14) /* version */ | (2u << 29) /* SWIZZLE_128B */;
+  const uint32_t hi = (sbo_bytes >> 4) | (1u << 14) /* version */ | (layout_type << 29);
   return (uint64_t)lo | ((uint64_t)hi << 32);
 }
 
@@ -124,7 +128,9 @@ struct KParams {
   Epilogue ep;
 };
 
-template <int BN>
+// EPI = false: raw accumulator store (split-K partials, dgrad, wgrad) — no epilogue code is compiled in.
+// EPI = true : bias / ReLU / Philox dropout / gate byte applied while the tile leaves TMEM.
+template <int BN, bool EPI>
 __global__ void __launch_bounds__(kThreads)
 tf32_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, KParams p) {
   extern __shared__ uint8_t smem_raw[];
@@ -192,8 +198,10 @@ tf32_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                            | (2u << 7) | (2u << 10)       // A, B format = TF32
                            | ((uint32_t)p.a_mn << 15) | ((uint32_t)p.b_mn << 16)
                            | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
-    const uint32_t a_lbo = p.a_mn ? 4096u : 16u, a_sbo = 1024u, a_adv = p.a_mn ? 1024u : (uint32_t)(UMMA_K * 4);
-    const uint32_t b_lbo = p.b_mn ? 4096u : 16u, b_sbo = 1024u, b_adv = p.b_mn ? 1024u : (uint32_t)(UMMA_K * 4);
+    const uint32_t a_lbo = p.a_mn ? 4096u : 16u, a_sbo = p.a_mn ? 512u : 1024u;
+    const uint32_t a_adv = p.a_mn ? 1024u : (uint32_t)(UMMA_K * 4), a_lt = p.a_mn ? 1u : 2u;
+    const uint32_t b_lbo = p.b_mn ? 4096u : 16u, b_sbo = p.b_mn ? 512u : 1024u;
+    const uint32_t b_adv = p.b_mn ? 1024u : (uint32_t)(UMMA_K * 4), b_lt = p.b_mn ? 1u : 2u;
     for (int i = 0; i < nkb; ++i) {
       const int s = i % stages;
       const uint32_t ph = (uint32_t)(i / stages) & 1u;
@@ -203,8 +211,8 @@ tf32_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       const uint32_t sb = sa + A_BYTES;
 #pragma unroll
       for (int k = 0; k < BK / UMMA_K; ++k) {
-        const uint64_t adesc = make_smem_desc(sa + k * a_adv, a_lbo, a_sbo);
-        const uint64_t bdesc = make_smem_desc(sb + k * b_adv, b_lbo, b_sbo);
+        const uint64_t adesc = make_smem_desc(sa + k * a_adv, a_lbo, a_sbo, a_lt);
+        const uint64_t bdesc = make_smem_desc(sb + k * b_adv, b_lbo, b_sbo, b_lt);
         umma_tf32(tmem_base, adesc, bdesc, idesc, (i > 0 || k > 0) ? 1u : 0u);
       }
       umma_commit(&empty_bar[s]);        // frees this smem stage when the MMAs above retire
@@ -231,7 +239,7 @@ tf32_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           const int n = n0 + c + j;
           if (n < p.N) {
             float v = __uint_as_float(r[j]);
-            if (p.splits == 1) v = apply_epilogue(v, p.ep, n, m, ld);
+            if (EPI) v = apply_epilogue(v, p.ep, n, m, ld);
             dst[(long long)n * ld + m] = v;
           }
         }
@@ -266,13 +274,13 @@ int get_encode() {
 
 // 2-D fp32 tensor map over a row-major [outer x inner] matrix with row stride ld (elements).
 int make_map(CUtensorMap* map, const float* base, long long inner, long long outer, long long ld, int box_inner,
-             int box_outer) {
+             int box_outer, CUtensorMapSwizzle swizzle) {
   cuuint64_t gdim[2] = {(cuuint64_t)inner, (cuuint64_t)outer};
   cuuint64_t gstr[1] = {(cuuint64_t)ld * 4ull};
   cuuint32_t box[2] = {(cuuint32_t)box_inner, (cuuint32_t)box_outer};
   cuuint32_t estr[2] = {1, 1};
   CUresult r = g_encode(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(base), gdim, gstr, box, estr,
-                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
     set_error("cuTensorMapEncodeTiled failed (CUresult %d) inner=%lld outer=%lld ld=%lld box=%dx%d", (int)r, inner,
@@ -282,13 +290,13 @@ int make_map(CUtensorMap* map, const float* base, long long inner, long long out
   return 0;
 }
 
-template <int BN>
+template <int BN, bool EPI>
 int launch_bn(const CUtensorMap& tmA, const CUtensorMap& tmB, const KParams& p, cudaStream_t stream) {
   const size_t stage_bytes = (size_t)(BM + BN) * BK * 4;
   const size_t smem = 1024 + (size_t)p.stages * stage_bytes + (2 * p.stages + 1) * 8 + 16;
   static bool attr_set = false;   // per template instance; benign race (idempotent)
   if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(tf32_gemm_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    cudaError_t e = cudaFuncSetAttribute(tf32_gemm_kernel<BN, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
     if (e != cudaSuccess) {
       set_error("cudaFuncSetAttribute(tf32_gemm_kernel) -> %s", cudaGetErrorString(e));
       return kCudaErrBase + (int)e;
@@ -296,7 +304,7 @@ int launch_bn(const CUtensorMap& tmA, const CUtensorMap& tmB, const KParams& p, 
     attr_set = true;
   }
   dim3 grid((p.M + BM - 1) / BM, (p.N + BN - 1) / BN, p.splits);
-  tf32_gemm_kernel<BN><<<grid, kThreads, smem, stream>>>(tmA, tmB, p);
+  tf32_gemm_kernel<BN, EPI><<<grid, kThreads, smem, stream>>>(tmA, tmB, p);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) {
     set_error("tf32_gemm_kernel<%d> launch (grid %d,%d,%d smem %zu) -> %s", BN, grid.x, grid.y, grid.z, smem,
@@ -321,9 +329,11 @@ int tf32_gemm_launch(const float* A, long long lda, int a_mn, const float* B, lo
   }
   const int BN = (N > 64) ? 128 : 64;
   CUtensorMap tmA, tmB;
-  rc = a_mn ? make_map(&tmA, A, M, R, lda, 32, 32) : make_map(&tmA, A, R, M, lda, BK, BM);
+  rc = a_mn ? make_map(&tmA, A, M, R, lda, 32, 32, CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B)
+            : make_map(&tmA, A, R, M, lda, BK, BM, CU_TENSOR_MAP_SWIZZLE_128B);
   if (rc) return rc;
-  rc = b_mn ? make_map(&tmB, B, N, R, ldb, 32, 32) : make_map(&tmB, B, R, N, ldb, BK, BN);
+  rc = b_mn ? make_map(&tmB, B, N, R, ldb, 32, 32, CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B)
+            : make_map(&tmB, B, R, N, ldb, BK, BN, CU_TENSOR_MAP_SWIZZLE_128B);
   if (rc) return rc;
   const int total_kb = (R + BK - 1) / BK;
   if (splits < 1) splits = 1;
@@ -334,6 +344,9 @@ int tf32_gemm_launch(const float* A, long long lda, int a_mn, const float* B, lo
   p.splits = (total_kb + p.kblocks_per_split - 1) / p.kblocks_per_split;   // no empty splits
   const int max_stages = (BN == 128) ? 6 : 8;
   p.stages = p.kblocks_per_split < max_stages ? p.kblocks_per_split : max_stages;
+  // short K loops (wgrad: K = batch): 2 stages keep the CTA at ~64 KB so 3 CTAs share an SM and one
+  // CTA's epilogue overlaps its neighbours' loads and MMAs
+  if (p.kblocks_per_split <= 8) p.stages = 2;
   if (p.stages < 2) p.stages = 2;
   p.a_mn = a_mn; p.b_mn = b_mn;
   p.out = out; p.ldo = ldo; p.ws = ws; p.ep = ep;
@@ -341,7 +354,9 @@ int tf32_gemm_launch(const float* A, long long lda, int a_mn, const float* B, lo
     set_error("tf32 gemm: split-K needs a workspace");
     return kInvalidArg;
   }
-  return BN == 128 ? launch_bn<128>(tmA, tmB, p, stream) : launch_bn<64>(tmA, tmB, p, stream);
+  const bool epi = p.splits == 1 && (ep.bias || ep.relu || ep.dropout || ep.gate);
+  if (BN == 128) return epi ? launch_bn<128, true>(tmA, tmB, p, stream) : launch_bn<128, false>(tmA, tmB, p, stream);
+  return epi ? launch_bn<64, true>(tmA, tmB, p, stream) : launch_bn<64, false>(tmA, tmB, p, stream);
 }
 
 }  // namespace b200

@@ -222,9 +222,10 @@ static inline int sgemm_effective_splits(int R, int splits) {
   return (R + per - 1) / per;
 }
 
-// pick a split count so that tiles * splits ~ one wave of 148 SMs, keeping >= 128 of K per split
+// pick a split count so that tiles * splits fits in ONE wave of 148 SMs (a 149th CTA would double the
+// kernel time: these kernels run one CTA per SM), keeping >= 128 of K per split
 static inline int pick_splits(int tiles, int R) {
-  int s = (kNumSMs + tiles - 1) / tiles;
+  int s = kNumSMs / tiles;
   if (s > 8) s = 8;
   const int max_by_k = R / 128 > 0 ? R / 128 : 1;
   if (s > max_by_k) s = max_by_k;
@@ -236,17 +237,18 @@ static inline int pick_splits(int tiles, int R) {
 // ------------------------------------------------------------------------------------------------
 constexpr int kSmallN = 16;
 
-__global__ void __launch_bounds__(128) linear_smalln_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w,
+// One CTA (8 warps) per batch row: warp w covers K-slice w, partial sums meet in shared memory.
+__global__ void __launch_bounds__(256) linear_smalln_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w,
                                                                 const float* __restrict__ bias, float* __restrict__ y,
                                                                 int B, int N, int K) {
-  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
-  if (warp >= B) return;
+  __shared__ float part[8][kSmallN];
+  const int b = blockIdx.x, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   float acc[kSmallN];
 #pragma unroll
   for (int n = 0; n < kSmallN; ++n) acc[n] = 0.f;
-  const float* xr = x + (long long)warp * K;
+  const float* xr = x + (long long)b * K;
   if ((K & 3) == 0 && (((uintptr_t)x | (uintptr_t)w) & 15) == 0) {
-    for (int k = lane * 4; k < K; k += 128) {
+    for (int k = (warp * 32 + lane) * 4; k < K; k += 256 * 4) {
       const float4 xv = *reinterpret_cast<const float4*>(xr + k);
 #pragma unroll
       for (int n = 0; n < kSmallN; ++n) {
@@ -257,7 +259,7 @@ __global__ void __launch_bounds__(128) linear_smalln_fwd_kernel(const float* __r
       }
     }
   } else {
-    for (int k = lane; k < K; k += 32) {
+    for (int k = warp * 32 + lane; k < K; k += 256) {
       const float xv = xr[k];
 #pragma unroll
       for (int n = 0; n < kSmallN; ++n)
@@ -268,8 +270,15 @@ __global__ void __launch_bounds__(128) linear_smalln_fwd_kernel(const float* __r
   for (int n = 0; n < kSmallN; ++n) {
     if (n < N) {
       const float s = warp_sum(acc[n]);
-      if (lane == 0) y[(long long)warp * N + n] = s + (bias ? bias[n] : 0.f);
+      if (lane == 0) part[warp][n] = s;
     }
+  }
+  __syncthreads();
+  if (threadIdx.x < N) {
+    float s = bias ? bias[threadIdx.x] : 0.f;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) s += part[j][threadIdx.x];
+    y[(long long)b * N + threadIdx.x] = s;
   }
 }
 
@@ -370,7 +379,7 @@ int b200ddp_linear_fwd(const float* x, const float* w, const float* bias, float*
   cudaStream_t s = as_stream(stream);
   if (N <= kSmallN) {
     B200_CHECK_ARG(!relu && dropout_p == 0.f && !gate, "linear_fwd: no epilogue on the small-N head");
-    linear_smalln_fwd_kernel<<<ceil_div((long long)B * 32, 128), 128, 0, s>>>(x, w, bias, y, B, N, K);
+    linear_smalln_fwd_kernel<<<B, 256, 0, s>>>(x, w, bias, y, B, N, K);
     B200_LAUNCH_OK();
     return 0;
   }

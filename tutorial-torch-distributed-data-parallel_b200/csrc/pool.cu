@@ -41,28 +41,39 @@ __global__ void __launch_bounds__(256) relu_maxpool_fwd_kernel(const float* __re
   }
 }
 
-// dx[b,c,h,w] = sum over the (<= 4) windows that cover (h,w) and selected it of dy[window]
+// dx[b,c,h,w] = sum over the (<= 4) windows that cover (h,w) and selected it of dy[window].
+// One CTA per (b,c) plane: the plane's dy and argmax codes (<= 27x27) are staged in shared memory, then
+// every input pixel gathers from them (deterministic, no atomics). 32-bit index math only.
+constexpr int kPoolMaxOut = 27 * 27;
 __global__ void __launch_bounds__(256) relu_maxpool_bwd_kernel(const float* __restrict__ dy,
                                                                const unsigned char* __restrict__ idx,
                                                                float* __restrict__ dx, long long planes, int H, int W,
                                                                int OH, int OW) {
-  const long long total = planes * H * W, stride = (long long)gridDim.x * blockDim.x;
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
-    const int w = (int)(i % W);
-    const long long t = i / W;
-    const int h = (int)(t % H);
-    const long long pl = t / H;
-    const int oh_lo = max(0, (h - (kPoolK - 1) + kPoolS - 1) / kPoolS), oh_hi = min(OH - 1, h / kPoolS);
-    const int ow_lo = max(0, (w - (kPoolK - 1) + kPoolS - 1) / kPoolS), ow_hi = min(OW - 1, w / kPoolS);
-    float g = 0.f;
-    for (int oh = oh_lo; oh <= oh_hi; ++oh)
-      for (int ow = ow_lo; ow <= ow_hi; ++ow) {
-        const long long o = (pl * OH + oh) * OW + ow;
-        const int code = idx[o];
-        const int kh = h - oh * kPoolS, kw = w - ow * kPoolS;
-        if (code == kh * kPoolK + kw) g += __ldg(dy + o);
-      }
-    dx[i] = g;
+  __shared__ float s_dy[kPoolMaxOut];
+  __shared__ unsigned char s_idx[kPoolMaxOut];
+  const int ohw = OH * OW, hw = H * W;
+  for (long long pl = blockIdx.x; pl < planes; pl += gridDim.x) {
+    const float* dyp = dy + pl * ohw;
+    const unsigned char* ip = idx + pl * ohw;
+    for (int i = threadIdx.x; i < ohw; i += blockDim.x) {
+      s_dy[i] = __ldg(dyp + i);
+      s_idx[i] = __ldg(ip + i);
+    }
+    __syncthreads();
+    float* dxp = dx + pl * hw;
+    for (int i = threadIdx.x; i < hw; i += blockDim.x) {
+      const int h = i / W, w = i - h * W;
+      const int oh_lo = max(0, (h - 1) >> 1), oh_hi = min(OH - 1, h >> 1);
+      const int ow_lo = max(0, (w - 1) >> 1), ow_hi = min(OW - 1, w >> 1);
+      float g = 0.f;
+      for (int oh = oh_lo; oh <= oh_hi; ++oh)
+        for (int ow = ow_lo; ow <= ow_hi; ++ow) {
+          const int o = oh * OW + ow;
+          if ((int)s_idx[o] == (h - 2 * oh) * kPoolK + (w - 2 * ow)) g += s_dy[o];
+        }
+      dxp[i] = g;
+    }
+    __syncthreads();
   }
 }
 
@@ -134,7 +145,9 @@ int b200ddp_relu_maxpool_bwd(const float* dy, const unsigned char* idx, float* d
   B200_DEVICE(device);
   const int OH = (H - kPoolK) / kPoolS + 1, OW = (W - kPoolK) / kPoolS + 1;
   const long long planes = (long long)B * C;
-  relu_maxpool_bwd_kernel<<<ew_grid(planes * H * W), 256, 0, as_stream(stream)>>>(dy, idx, dx, planes, H, W, OH, OW);
+  B200_CHECK_ARG(OH * OW <= kPoolMaxOut, "relu_maxpool_bwd: pooled plane %dx%d exceeds %d elements", OH, OW, kPoolMaxOut);
+  const int grid = (int)(planes < (long long)kNumSMs * 16 ? planes : (long long)kNumSMs * 16);
+  relu_maxpool_bwd_kernel<<<grid, 256, 0, as_stream(stream)>>>(dy, idx, dx, planes, H, W, OH, OW);
   B200_LAUNCH_OK();
   return 0;
 }
