@@ -149,3 +149,38 @@ yb = torch.empty_like(xb)
 wbn = torch.ones(C, device=DEV)
 timeit("bn_elemt [128,64,55,55]", lambda: chk(L.b200ddp_bn_elemt(xb.data_ptr(), stats.data_ptr(), stats.data_ptr() + 4 * C, wbn.data_ptr(),
                                                                 wbn.data_ptr(), yb.data_ptr(), B, C, HW, 1, 0, st()), "bne"), 8.0 * xb.numel())
+
+# ---- convolutions (implicit GEMM, tcgen05 TF32) ---------------------------------------------------------------------------
+from b200ddp import nn as bnn  # noqa: E402
+
+for (Cin, H, Cout, K, s_, p_, tag) in ((3, 224, 64, 11, 4, 2, "conv1"), (64, 27, 192, 5, 1, 2, "conv2"), (192, 13, 384, 3, 1, 1, "conv3"),
+                                       (384, 13, 256, 3, 1, 1, "conv4"), (256, 13, 256, 3, 1, 1, "conv5")):
+    xin = torch.randn(B, Cin, H, H, device=DEV)
+    conv = bnn.Conv2d(Cin, Cout, K, stride=s_, padding=p_).to(DEV)
+    OH = (H + 2 * p_ - K) // s_ + 1
+    Kk = Cin * K * K
+    fl = 2.0 * B * OH * OH * Cout * Kk
+    w = conv.weight.detach()
+    if Kk % 4:
+        ldw = (Kk + 31) // 32 * 32
+        wmat = torch.zeros(Cout, ldw, device=DEV)
+        wmat[:, :Kk] = w.reshape(Cout, Kk)
+    else:
+        ldw, wmat = Kk, w
+    bias = conv.bias.detach()
+    yb_ = 4.0 * (xin.numel() + B * Cout * OH * OH + w.numel())
+    timeit(f"conv2d_fwd {tag}", lambda: bnn.conv2d_forward_raw(xin, wmat, ldw, bias, Cout, K, K, s_, p_, False), yb_, fl)
+    dyc = torch.randn(B, Cout, OH, OH, device=DEV)
+    dwc = torch.empty_like(w)
+    koff, kpos = bnn._conv_tables(DEV, Cin, H, H, K, K)
+    nb = int(L.b200ddp_conv2d_wgrad_workspace_bytes(B, Cin, H, H, Cout, K, K, s_, p_))
+    wsc = torch.empty(max(nb, 256), dtype=torch.uint8, device=DEV)
+    timeit(f"conv2d_wgrad {tag} (incl. split finalize)",
+           lambda: chk(L.b200ddp_conv2d_wgrad(xin.data_ptr(), dyc.data_ptr(), dwc.data_ptr(), koff.data_ptr(), kpos.data_ptr(), B, Cin, H, H,
+                                              Cout, K, K, s_, p_, wsc.data_ptr(), wsc.numel(), 0, st()), "wgrad"), yb_, fl)
+    if s_ == 1:
+        kt = Cout * K * K
+        wt = torch.empty(Cin, kt, device=DEV)
+        chk(L.b200ddp_conv2d_weight_prep(w.data_ptr(), wt.data_ptr(), Cout, Cin, K, K, kt, 1, 0, st()), "prep")
+        timeit(f"conv2d_dgrad {tag}", lambda: bnn.conv2d_forward_raw(dyc, wt, kt, None, Cin, K, K, 1, K - 1 - p_, False), yb_, fl)
+    del xin, dyc

@@ -1,0 +1,109 @@
+"""C1-C5: the implicit-GEMM tcgen05 convolution kernels through the C ABI against float64 torch convolutions
+(the published definition of nn.Conv2d), at the toy model's five layer shapes, with ragged pixel counts,
+bias + ReLU epilogues, dgrad (flipped-weight forward) and split-K wgrad.
+
+Tolerance: TF32 operands (fp32 truncated to 10 mantissa bits), fp32 accumulation -> 3e-3 of the output scale,
+the same bound as the TF32 Linear kernels and the numeric class the reference itself uses for convolutions
+(cuDNN TF32)."""
+import pytest
+import torch
+
+import b200ddp
+from b200ddp import _lib
+from b200ddp import nn as bnn
+
+pytestmark = pytest.mark.gpu
+DEV = torch.device("cuda", 0)
+TOL = 3e-3
+
+#           Cin  H   Cout K  s  p
+LAYERS = [(3, 224, 64, 11, 4, 2), (64, 27, 192, 5, 1, 2), (192, 13, 384, 3, 1, 1), (384, 13, 256, 3, 1, 1),
+          (256, 13, 256, 3, 1, 1)]
+
+
+def _err(got, want):
+    return float((got.double() - want).abs().max() / want.abs().max().clamp_min(1e-30))
+
+
+@pytest.mark.parametrize("layer", range(5))
+@pytest.mark.parametrize("batch", [4, 5])
+def test_conv_forward_matches_float64(layer, batch):
+    Cin, H, Cout, K, s, p = LAYERS[layer]
+    torch.manual_seed(layer * 10 + batch)
+    x = torch.randn(batch, Cin, H, H, device=DEV)
+    conv = bnn.Conv2d(Cin, Cout, K, stride=s, padding=p, relu=(layer in (2, 3))).to(DEV)
+    y = conv(x)
+    ref = torch.nn.functional.conv2d(x.double(), conv.weight.double(), conv.bias.double(), stride=s, padding=p)
+    if conv.relu:
+        ref = torch.relu(ref)
+    assert y.shape == ref.shape
+    assert _err(y, ref) < TOL
+
+
+@pytest.mark.parametrize("layer", range(5))
+def test_conv_backward_matches_float64(layer):
+    Cin, H, Cout, K, s, p = LAYERS[layer]
+    batch = 6
+    torch.manual_seed(100 + layer)
+    x = torch.randn(batch, Cin, H, H, device=DEV, requires_grad=(layer > 0))
+    conv = bnn.Conv2d(Cin, Cout, K, stride=s, padding=p).to(DEV)
+    y = conv(x)
+    dy = torch.randn_like(y)
+    y.backward(dy)
+    x64 = x.detach().double().requires_grad_(layer > 0)
+    w64 = conv.weight.detach().double().requires_grad_()
+    b64 = conv.bias.detach().double().requires_grad_()
+    torch.nn.functional.conv2d(x64, w64, b64, stride=s, padding=p).backward(dy.double())
+    assert _err(conv.weight.grad, w64.grad) < TOL
+    assert _err(conv.bias.grad, b64.grad) < 1e-5
+    if layer > 0:
+        assert _err(x.grad, x64.grad) < TOL
+
+
+def test_conv_full_batch_first_layer_and_relu_backward():
+    """Batch 128 at conv1 (3025 CTAs, 49-way split wgrad) and a fused-ReLU layer's backward mask."""
+    torch.manual_seed(7)
+    x = torch.randn(128, 3, 224, 224, device=DEV)
+    conv = bnn.Conv2d(3, 64, 11, stride=4, padding=2).to(DEV)
+    y = conv(x)
+    dy = torch.randn_like(y)
+    y.backward(dy)
+    ref = torch.nn.Conv2d(3, 64, 11, stride=4, padding=2).to(DEV).double()
+    ref.load_state_dict({k: v.double() for k, v in conv.state_dict().items()})
+    y64 = ref(x.double())
+    y64.backward(dy.double())
+    assert _err(y, y64.detach()) < TOL
+    assert _err(conv.weight.grad, ref.weight.grad) < TOL
+    assert _err(conv.bias.grad, ref.bias.grad) < 1e-5
+    xr = torch.randn(8, 192, 13, 13, device=DEV, requires_grad=True)
+    c3 = bnn.Conv2d(192, 384, 3, padding=1, relu=True).to(DEV)
+    out = c3(xr)
+    g = torch.randn_like(out)
+    out.backward(g)
+    x64 = xr.detach().double().requires_grad_()
+    o64 = torch.relu(torch.nn.functional.conv2d(x64, c3.weight.double(), c3.bias.double(), padding=1))
+    o64.backward(g.double())
+    sure = (o64.detach().abs() > 1e-2)          # away from the ReLU kink
+    assert float(((out > 0) != (o64 > 0))[sure].sum()) == 0
+    rel_l2 = float((xr.grad.double() - x64.grad).norm() / x64.grad.norm())
+    assert rel_l2 < 2e-2                          # a few ReLU gates flip near zero (TF32 forward)
+
+
+def test_weight_prep_and_channel_sum_exact():
+    L = _lib.load()
+    st = torch.cuda.current_stream(DEV).cuda_stream
+    w = torch.randn(7, 5, 3, 3, device=DEV)
+    out = torch.empty(5, 7 * 9, device=DEV)
+    _lib.check(L.b200ddp_conv2d_weight_prep(w.data_ptr(), out.data_ptr(), 7, 5, 3, 3, 63, 1, 0, st), "prep")
+    want = w.flip(2, 3).permute(1, 0, 2, 3).reshape(5, 63)
+    assert torch.equal(out, want)
+    pad = torch.empty(7, 48, device=DEV)
+    _lib.check(L.b200ddp_conv2d_weight_prep(w.data_ptr(), pad.data_ptr(), 7, 5, 3, 3, 48, 0, 0, st), "prep0")
+    assert torch.equal(pad[:, :45], w.reshape(7, 45)) and float(pad[:, 45:].abs().sum()) == 0
+    dy = torch.randn(9, 64, 55, 55, device=DEV)
+    res = torch.empty(64, device=DEV)
+    scratch = torch.zeros(int(L.b200ddp_channel_sum_scratch_bytes(9, 64)), dtype=torch.uint8, device=DEV)
+    for _ in range(2):
+        _lib.check(L.b200ddp_channel_sum(dy.data_ptr(), res.data_ptr(), 9, 64, 55 * 55, scratch.data_ptr(),
+                                         scratch.numel(), 0, st), "chsum")
+        assert torch.allclose(res.double(), dy.double().sum((0, 2, 3)), rtol=1e-5, atol=1e-3)

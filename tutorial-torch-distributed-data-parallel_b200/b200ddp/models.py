@@ -11,8 +11,8 @@ several stock layers; the layers they absorb stay in the Sequential as `nn.Ident
   avgpool:    AdaptiveAvgPool2d((6,6)) — the identity at 224x224 input, skipped when the map is already 6x6
   classifier: 0 Dropout*      1 Linear+ReLU+Dropout*  2,3 (fused)  4 Linear+ReLU*  5 (fused)  6 Linear* (head)
 
-(* = b200ddp kernels.) The five convolutions still run through torch (cuDNN) in this round — see
-DESIGN.md; everything else on the model's path is a hand-written sm_100a kernel.
+(* = b200ddp kernels.) The five convolutions are b200ddp implicit-GEMM tcgen05 kernels too (`conv="b200"`,
+default; conv 6 and 8 fold their ReLU into the epilogue); `conv="cudnn"` keeps torch.nn.Conv2d for A/B runs.
 
 `hidden` scales classifier.1/.4 (BASELINE config 5), `bn=True` builds the AlexNet-BN variant of
 SURVEY 8(d) config 4 (BatchNorm2d after each conv, before its ReLU).
@@ -27,10 +27,25 @@ from . import nn as bnn
 
 class AlexNet(nn.Module):
     def __init__(self, num_classes: int = 10, hidden: int = 4096, dropout: float = 0.5, bn: bool = False,
-                 mode="tf32") -> None:
+                 mode="tf32", conv: str = "b200") -> None:
         super().__init__()
         self.bn = bn
-        if not bn:
+        if conv not in ("b200", "cudnn"):
+            raise ValueError("conv must be 'b200' (own implicit-GEMM kernels) or 'cudnn' (torch.nn.Conv2d)")
+        if not bn and conv == "b200":
+            self.features = nn.Sequential(
+                bnn.Conv2d(3, 64, kernel_size=11, stride=4, padding=2),
+                bnn.ReLUMaxPool2d(), nn.Identity(),
+                bnn.Conv2d(64, 192, kernel_size=5, padding=2),
+                bnn.ReLUMaxPool2d(), nn.Identity(),
+                bnn.Conv2d(192, 384, kernel_size=3, padding=1, relu=True),
+                nn.Identity(),
+                bnn.Conv2d(384, 256, kernel_size=3, padding=1, relu=True),
+                nn.Identity(),
+                bnn.Conv2d(256, 256, kernel_size=3, padding=1),
+                bnn.ReLUMaxPool2d(), nn.Identity(),
+            )
+        elif not bn:
             self.features = nn.Sequential(
                 nn.Conv2d(3, 64, kernel_size=11, stride=4, padding=2),
                 bnn.ReLUMaxPool2d(), nn.Identity(),
@@ -45,7 +60,8 @@ class AlexNet(nn.Module):
             )
         else:
             def block(cin, cout, k, s, p, pool):
-                layers = [nn.Conv2d(cin, cout, kernel_size=k, stride=s, padding=p), nn.BatchNorm2d(cout), nn.ReLU(inplace=True)]
+                conv_cls = bnn.Conv2d if conv == "b200" else nn.Conv2d
+                layers = [conv_cls(cin, cout, kernel_size=k, stride=s, padding=p), nn.BatchNorm2d(cout), nn.ReLU(inplace=True)]
                 if pool:
                     layers.append(nn.MaxPool2d(kernel_size=3, stride=2))
                 return layers
@@ -79,9 +95,9 @@ def fuse_bn_relu(model: AlexNet) -> AlexNet:
 
 
 def load_model(num_classes: int = 10, hidden: int = 4096, seed: int | None = None, mode="tf32", bn: bool = False,
-               dropout: float = 0.5) -> AlexNet:
+               dropout: float = 0.5, conv: str = "b200") -> AlexNet:
     """Counterpart of reference data_and_toy_model.py:41-45. The reference downloads ImageNet weights
     (no network here): weights are torch's default random init, optionally under `seed`."""
     if seed is not None:
         torch.manual_seed(seed)
-    return AlexNet(num_classes=num_classes, hidden=hidden, dropout=dropout, bn=bn, mode=mode)
+    return AlexNet(num_classes=num_classes, hidden=hidden, dropout=dropout, bn=bn, mode=mode, conv=conv)

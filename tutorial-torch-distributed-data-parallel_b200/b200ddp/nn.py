@@ -140,6 +140,127 @@ class Linear(nn.Linear):
 
 
 # ---------------------------------------------------------------------------------------------------------
+# Conv2d (+ bias + ReLU) as an implicit GEMM on tcgen05 (csrc/conv.cu)
+# ---------------------------------------------------------------------------------------------------------
+_CONV_TABLES: dict = {}
+
+
+def _conv_tables(device, Cin: int, H: int, W: int, KH: int, KW: int):
+    """int32 device tables indexed by k = (ci, kh, kw): input offset and packed window position.
+    Padded to a multiple of 128 entries with an 'invalid' marker (host logic; built once per shape)."""
+    key = (str(device), Cin, H, W, KH, KW)
+    t = _CONV_TABLES.get(key)
+    if t is None:
+        K = Cin * KH * KW
+        kp = (K + 127) // 128 * 128
+        k = torch.arange(kp, dtype=torch.int64)
+        ci, rem = k // (KH * KW), k % (KH * KW)
+        kh, kw = rem // KW, rem % KW
+        koff = (ci * H * W + kh * W + kw).to(torch.int32)
+        kpos = (kh | (kw << 16)).to(torch.int32)
+        koff[K:] = 0
+        kpos[K:] = 0x7FFF7FFF
+        t = (koff.to(device), kpos.to(device))
+        _CONV_TABLES[key] = t
+    return t
+
+
+def conv2d_forward_raw(x, wmat, ldw, bias, Cout, KH, KW, stride, pad, relu):
+    """y = conv(x, wmat) through b200ddp_conv2d_fwd; x [N,Cin,H,W] contiguous fp32 CUDA."""
+    L = _lib.load()
+    N, Cin, H, W = x.shape
+    OH, OW = (H + 2 * pad - KH) // stride + 1, (W + 2 * pad - KW) // stride + 1
+    koff, kpos = _conv_tables(x.device, Cin, H, W, KH, KW)
+    y = torch.empty((N, Cout, OH, OW), dtype=torch.float32, device=x.device)
+    _lib.check(L.b200ddp_conv2d_fwd(x.data_ptr(), wmat.data_ptr(), int(ldw), _lib.ptr(bias), y.data_ptr(),
+                                    koff.data_ptr(), kpos.data_ptr(), N, Cin, H, W, Cout, KH, KW, stride, pad,
+                                    int(bool(relu)), _lib.dev_index(x), _lib.cur_stream(x.device)), "conv2d_fwd")
+    return y
+
+
+class _Conv2dFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, weight, bias, stride, pad, relu):
+        L = _lib.load()
+        x = _lib.f32c(x, "input")
+        w = _lib.f32c(weight, "weight")
+        Cout, Cin, KH, KW = w.shape
+        if x.shape[1] != Cin:
+            raise ValueError(f"Conv2d: input has {x.shape[1]} channels, weight expects {Cin}")
+        K = Cin * KH * KW
+        if K % 4 == 0 and w.data_ptr() % 16 == 0:
+            wmat, ldw = w, K
+        else:   # TMA needs 16-byte aligned rows: zero-padded copy (conv1: K = 363)
+            ldw = (K + 31) // 32 * 32
+            wmat = torch.empty((Cout, ldw), dtype=torch.float32, device=x.device)
+            _lib.check(L.b200ddp_conv2d_weight_prep(w.data_ptr(), wmat.data_ptr(), Cout, Cin, KH, KW, ldw, 0,
+                                                    _lib.dev_index(x), _lib.cur_stream(x.device)), "weight_prep")
+        y = conv2d_forward_raw(x, wmat, ldw, bias, Cout, KH, KW, stride, pad, relu)
+        ctx.save_for_backward(x, w, y if relu else None)
+        ctx.stride, ctx.pad, ctx.relu = stride, pad, relu
+        ctx.weight_param, ctx.bias_param = weight, bias
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        L = _lib.load()
+        x, w, y_relu = ctx.saved_tensors
+        dev, st = _lib.dev_index(x), _lib.cur_stream(x.device)
+        N, Cin, H, W = x.shape
+        Cout, _, KH, KW = w.shape
+        stride, pad = ctx.stride, ctx.pad
+        OH, OW = (H + 2 * pad - KH) // stride + 1, (W + 2 * pad - KW) // stride + 1
+        dy = _lib.f32c(dy, "grad_output")
+        if y_relu is not None:
+            dz = torch.empty_like(dy)
+            _lib.check(L.b200ddp_relu_bwd(dy.data_ptr(), y_relu.data_ptr(), dz.data_ptr(), dy.numel(), dev, st), "relu_bwd")
+        else:
+            dz = dy
+        db = None
+        if ctx.bias_param is not None and ctx.needs_input_grad[2]:
+            db = _grad_target(ctx.bias_param, (Cout,), x.device)
+            nb = int(L.b200ddp_channel_sum_scratch_bytes(N, Cout))
+            scratch = _lib.workspace(x.device, nb, "chsum", zero=True)
+            _lib.check(L.b200ddp_channel_sum(dz.data_ptr(), db.data_ptr(), N, Cout, OH * OW, scratch.data_ptr(),
+                                             scratch.numel(), dev, st), "channel_sum")
+        dw = None
+        if ctx.needs_input_grad[1]:
+            dw = _grad_target(ctx.weight_param, tuple(w.shape), x.device)
+            koff, kpos = _conv_tables(x.device, Cin, H, W, KH, KW)
+            nb = int(L.b200ddp_conv2d_wgrad_workspace_bytes(N, Cin, H, W, Cout, KH, KW, stride, pad))
+            ws = _lib.workspace(x.device, max(nb, 256), "conv_wgrad")
+            _lib.check(L.b200ddp_conv2d_wgrad(x.data_ptr(), dz.data_ptr(), dw.data_ptr(), koff.data_ptr(),
+                                              kpos.data_ptr(), N, Cin, H, W, Cout, KH, KW, stride, pad, ws.data_ptr(),
+                                              ws.numel(), dev, st), "conv2d_wgrad")
+        dx = None
+        if ctx.needs_input_grad[0]:
+            if stride != 1:
+                raise NotImplementedError("b200ddp Conv2d: input gradients are implemented for stride 1 only "
+                                          "(the toy model's strided conv is its first layer)")
+            kt = Cout * KH * KW
+            wt = torch.empty((Cin, kt), dtype=torch.float32, device=x.device)
+            _lib.check(L.b200ddp_conv2d_weight_prep(w.data_ptr(), wt.data_ptr(), Cout, Cin, KH, KW, kt, 1, dev, st),
+                       "weight_prep")
+            dx = conv2d_forward_raw(dz, wt, kt, None, Cin, KH, KW, 1, KH - 1 - pad, False)
+        return dx, dw, db, None, None, None
+
+
+class Conv2d(nn.Conv2d):
+    """nn.Conv2d (square stride / padding, no dilation / groups) with the following ReLU optionally folded in."""
+
+    def __init__(self, in_channels, out_channels, kernel_size, stride=1, padding=0, bias=True, relu=False, device=None,
+                 dtype=None) -> None:
+        super().__init__(in_channels, out_channels, kernel_size, stride=stride, padding=padding, bias=bias,
+                         device=device, dtype=dtype)
+        if self.stride[0] != self.stride[1] or self.padding[0] != self.padding[1]:
+            raise ValueError("b200ddp Conv2d needs equal stride / padding in both dimensions")
+        self.relu = bool(relu)
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        return _Conv2dFn.apply(x, self.weight, self.bias, self.stride[0], self.padding[0], self.relu)
+
+
+# ---------------------------------------------------------------------------------------------------------
 # softmax cross-entropy
 # ---------------------------------------------------------------------------------------------------------
 class _CrossEntropyFn(torch.autograd.Function):

@@ -1,6 +1,7 @@
 // Private interface between the linear-layer entry points (linear.cu) and the two GEMM
 // engines: the strict-fp32 SIMT kernel (linear.cu) and the TF32 tcgen05/TMA kernel (gemm_tf32.cu).
 #pragma once
+#include <cuda.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 
@@ -44,6 +45,11 @@ __device__ __forceinline__ float apply_epilogue(float v, const Epilogue& ep, lon
 int tf32_gemm_launch(const float* A, long long lda, int a_mn_major, const float* B, long long ldb,
                      int b_mn_major, int M, int N, int R, float* out, long long ldo, int splits, float* ws,
                      const Epilogue& ep, cudaStream_t stream);
+
+// 2-D fp32 TMA tensor map over a row-major [outer x inner] matrix with row stride ld (elements).
+// swizzle_base32b = 0: SWIZZLE_128B (K-major operands); 1: SWIZZLE_128B_ATOM_32B (MN-major 32-bit operands).
+int tma_map_2d(CUtensorMap* map, const float* base, long long inner, long long outer, long long ld, int box_inner,
+               int box_outer, int swizzle_base32b);
 
 // Number of K splits tf32_gemm_launch will really use for a request (no empty splits).
 inline int tf32_effective_splits(int R, int splits) {

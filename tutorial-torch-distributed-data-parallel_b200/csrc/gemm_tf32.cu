@@ -17,6 +17,7 @@
 // One CTA computes one 128 x BN output tile for one K split. Warp roles: warp 0 = TMA producer,
 // warp 1 = TMEM allocator + single-thread MMA issuer, warps 2..5 = epilogue (TMEM lane quarters).
 #include "gemm.h"
+#include "tc.cuh"
 
 #include <cuda.h>
 #include <cudaTypedefs.h>
@@ -27,95 +28,12 @@ namespace b200 {
 
 namespace {
 
+using namespace tc;
+
 constexpr int BM = 128;          // UMMA_M (cta_group::1)
 constexpr int BK = 32;           // fp32 elements per k-block = one 128-byte swizzle span
 constexpr int UMMA_K = 8;        // kind::tf32: 32 bytes of K per instruction
 constexpr int kThreads = 192;
-constexpr uint32_t kSpinLimit = 1u << 28;  // bounded waits: trap instead of hanging the GPU box
-
-__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-
-__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
-  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
-}
-__device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t* bar, uint32_t bytes) {
-  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
-  const uint32_t addr = smem_u32(bar);
-  uint32_t done = 0, spins = 0;
-  while (true) {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-        "selp.u32 %0, 1, 0, p;\n\t}"
-        : "=r"(done)
-        : "r"(addr), "r"(parity)
-        : "memory");
-    if (done) break;
-    if (++spins > kSpinLimit) {
-      printf("b200ddp tf32 gemm: mbarrier wait timed out (block %d,%d,%d thread %d)\n", blockIdx.x, blockIdx.y,
-             blockIdx.z, threadIdx.x);
-      __trap();
-    }
-  }
-}
-__device__ __forceinline__ void tma_load_2d(void* smem_dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1) {
-  asm volatile(
-      "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
-      ::"r"(smem_u32(smem_dst)), "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
-      : "memory");
-}
-__device__ __forceinline__ void tmem_alloc(uint32_t* slot, uint32_t ncols) {
-  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(slot)), "r"(ncols) : "memory");
-  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
-}
-__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t ncols) {
-  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
-}
-__device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
-  asm volatile(
-      "{\n\t.reg .pred p;\n\t"
-      "setp.ne.b32 p, %4, 0;\n\t"
-      "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
-      ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
-      : "memory");
-}
-__device__ __forceinline__ void umma_commit(uint64_t* bar) {
-  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
-}
-__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
-
-// 32 lanes x 32 consecutive fp32 columns of TMEM -> 32 registers per thread.
-__device__ __forceinline__ void tmem_ld_32x32(uint32_t taddr, uint32_t (&r)[32]) {
-  asm volatile(
-      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
-      "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,"
-      "%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
-      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
-        "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
-        "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
-        "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
-      : "r"(taddr)
-      : "memory");
-  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-}
-
-// Shared-memory matrix descriptor (sm_100 format, version 1).
-//   K-major tile  [rows][32 fp32], SWIZZLE_128B (layout type 2): 8-row groups are 1024 B apart (SBO);
-//                  LBO unused (1).
-//   MN-major tile, 32-bit operands: the only legal layout is SWIZZLE_128B_BASE32B (layout type 1; TMA
-//                  swizzle 128B_ATOM_32B): rows of 32 MN-contiguous elements (128 B) whose 32-byte chunks
-//                  are XOR-ed with (row % 4); a k-group is 4 rows = 512 B (SBO); the next 32-element MN
-//                  atom is +4096 B (LBO) because each TMA box holds 32 k-rows x 128 B.
-__device__ __forceinline__ uint64_t make_smem_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes,
-                                                   uint32_t layout_type) {
-  const uint32_t lo = ((saddr & 0x3FFFFu) >> 4) | ((lbo_bytes >> 4) << 16);
-  const uint32_t hi = (sbo_bytes >> 4) | (1u << 14) /* version */ | (layout_type << 29);
-  return (uint64_t)lo | ((uint64_t)hi << 32);
-}
-
 struct KParams {
   int M, N, R;
   int kblocks_per_split;
@@ -147,12 +65,11 @@ tf32_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int m0 = blockIdx.x * BM, n0 = blockIdx.y * BN, z = blockIdx.z;
+  // Split-K is INTERLEAVED: split z owns k-blocks z, z+splits, z+2*splits, ... so that the CTAs working on the
+  // same rows of the streamed operand touch adjacent 128-byte pieces at the same time (DRAM page locality)
+  // instead of 'splits' far-apart column ranges.
   const int total_kb = (p.R + BK - 1) / BK;
-  const int kb_begin = z * p.kblocks_per_split;
-  int kb_end = kb_begin + p.kblocks_per_split;
-  if (kb_end > total_kb) kb_end = total_kb;
-  const int nkb = kb_end - kb_begin;   // host guarantees >= 1
-
+  const int nkb = (total_kb - z + p.splits - 1) / p.splits;   // host guarantees splits <= total_kb
   if (warp == 0 && lane == 0) {
     for (int s = 0; s < stages; ++s) {
       mbar_init(&full_bar[s], 1);
@@ -178,7 +95,7 @@ tf32_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       mbar_arrive_expect_tx(&full_bar[s], STAGE_BYTES);
       uint8_t* sa = smem + (size_t)s * STAGE_BYTES;
       uint8_t* sb = sa + A_BYTES;
-      const int r0 = (kb_begin + i) * BK;
+      const int r0 = (z + i * p.splits) * BK;
       if (!p.a_mn) {
         tma_load_2d(sa, &tmA, &full_bar[s], r0, m0);                       // box {32 r, 128 m}
       } else {
@@ -254,10 +171,12 @@ tf32_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 // ------------------------------------------------------------------------------------------------
 // host side
 // ------------------------------------------------------------------------------------------------
-PFN_cuTensorMapEncodeTiled_v12000 g_encode = nullptr;
-std::once_flag g_encode_once;
+}  // namespace
 
-int get_encode() {
+static PFN_cuTensorMapEncodeTiled_v12000 g_encode = nullptr;
+static std::once_flag g_encode_once;
+
+static int get_encode() {
   std::call_once(g_encode_once, [] {
     void* fn = nullptr;
     cudaDriverEntryPointQueryResult qres;
@@ -273,8 +192,11 @@ int get_encode() {
 }
 
 // 2-D fp32 tensor map over a row-major [outer x inner] matrix with row stride ld (elements).
-int make_map(CUtensorMap* map, const float* base, long long inner, long long outer, long long ld, int box_inner,
-             int box_outer, CUtensorMapSwizzle swizzle) {
+int tma_map_2d(CUtensorMap* map, const float* base, long long inner, long long outer, long long ld, int box_inner,
+               int box_outer, int swizzle_base32b) {
+  int rc0 = get_encode();
+  if (rc0) return rc0;
+  const CUtensorMapSwizzle swizzle = swizzle_base32b ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B;
   cuuint64_t gdim[2] = {(cuuint64_t)inner, (cuuint64_t)outer};
   cuuint64_t gstr[1] = {(cuuint64_t)ld * 4ull};
   cuuint32_t box[2] = {(cuuint32_t)box_inner, (cuuint32_t)box_outer};
@@ -289,6 +211,8 @@ int make_map(CUtensorMap* map, const float* base, long long inner, long long out
   }
   return 0;
 }
+
+namespace {
 
 template <int BN, bool EPI>
 int launch_bn(const CUtensorMap& tmA, const CUtensorMap& tmB, const KParams& p, cudaStream_t stream) {
@@ -320,8 +244,7 @@ int launch_bn(const CUtensorMap& tmA, const CUtensorMap& tmB, const KParams& p, 
 int tf32_gemm_launch(const float* A, long long lda, int a_mn, const float* B, long long ldb, int b_mn, int M, int N,
                      int R, float* out, long long ldo, int splits, float* ws, const Epilogue& ep,
                      cudaStream_t stream) {
-  int rc = get_encode();
-  if (rc) return rc;
+  int rc = 0;
   if ((((uintptr_t)A | (uintptr_t)B) & 15) || (lda & 3) || (ldb & 3)) {
     set_error("tf32 gemm: operands must be 16-byte aligned with leading dimensions multiple of 4 (lda=%lld ldb=%lld)",
               lda, ldb);
@@ -329,11 +252,9 @@ int tf32_gemm_launch(const float* A, long long lda, int a_mn, const float* B, lo
   }
   const int BN = (N > 64) ? 128 : 64;
   CUtensorMap tmA, tmB;
-  rc = a_mn ? make_map(&tmA, A, M, R, lda, 32, 32, CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B)
-            : make_map(&tmA, A, R, M, lda, BK, BM, CU_TENSOR_MAP_SWIZZLE_128B);
+  rc = a_mn ? tma_map_2d(&tmA, A, M, R, lda, 32, 32, 1) : tma_map_2d(&tmA, A, R, M, lda, BK, BM, 0);
   if (rc) return rc;
-  rc = b_mn ? make_map(&tmB, B, N, R, ldb, 32, 32, CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B)
-            : make_map(&tmB, B, R, N, ldb, BK, BN, CU_TENSOR_MAP_SWIZZLE_128B);
+  rc = b_mn ? tma_map_2d(&tmB, B, N, R, ldb, 32, 32, 1) : tma_map_2d(&tmB, B, R, N, ldb, BK, BN, 0);
   if (rc) return rc;
   const int total_kb = (R + BK - 1) / BK;
   if (splits < 1) splits = 1;

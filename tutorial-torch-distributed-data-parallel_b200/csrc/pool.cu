@@ -61,17 +61,22 @@ __global__ void __launch_bounds__(256) relu_maxpool_bwd_kernel(const float* __re
     }
     __syncthreads();
     float* dxp = dx + pl * hw;
-    for (int i = threadIdx.x; i < hw; i += blockDim.x) {
-      const int h = i / W, w = i - h * W;
-      const int oh_lo = max(0, (h - 1) >> 1), oh_hi = min(OH - 1, h >> 1);
-      const int ow_lo = max(0, (w - 1) >> 1), ow_hi = min(OW - 1, w >> 1);
-      float g = 0.f;
-      for (int oh = oh_lo; oh <= oh_hi; ++oh)
-        for (int ow = ow_lo; ow <= ow_hi; ++ow) {
-          const int o = oh * OW + ow;
-          if ((int)s_idx[o] == (h - 2 * oh) * kPoolK + (w - 2 * ow)) g += s_dy[o];
-        }
-      dxp[i] = g;
+    // warp <-> input row, lane <-> column: no integer division, straight-line window tests. A pixel (h,w) lies
+    // in window rows {h>>1} and, when h is even, {(h>>1)-1} (same for columns): at most 2x2 candidates.
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
+    for (int h = warp; h < H; h += nwarps) {
+      const int oh1 = h >> 1, oh0 = oh1 - 1, hodd = h & 1;
+      const bool vh1 = oh1 < OH, vh0 = !hodd && oh0 >= 0;
+      for (int w = lane; w < W; w += 32) {
+        const int ow1 = w >> 1, ow0 = ow1 - 1, wodd = w & 1;
+        const bool vw1 = ow1 < OW, vw0 = !wodd && ow0 >= 0;
+        float g = 0.f;
+        if (vh1 && vw1) { const int o = oh1 * OW + ow1; if ((int)s_idx[o] == hodd * 3 + wodd) g += s_dy[o]; }
+        if (vh1 && vw0) { const int o = oh1 * OW + ow0; if ((int)s_idx[o] == hodd * 3 + 2) g += s_dy[o]; }
+        if (vh0 && vw1) { const int o = oh0 * OW + ow1; if ((int)s_idx[o] == 6 + wodd) g += s_dy[o]; }
+        if (vh0 && vw0) { const int o = oh0 * OW + ow0; if ((int)s_idx[o] == 8) g += s_dy[o]; }
+        dxp[h * W + w] = g;
+      }
     }
     __syncthreads();
   }
