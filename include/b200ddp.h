@@ -117,20 +117,23 @@ int b200ddp_softmax_ce(const float* logits, const long long* labels, float* loss
 /* Replace nn.Conv2d forward / backward (cuDNN TF32 implicit GEMM + NCHW<->NHWC conversions) of torchvision
  * alexnet.py:22,25,28,30,32, reached from reference :121 / :125. x [Nb][Cin][H][W], y [Nb][Cout][OH][OW], fp32 NCHW.
  * wmat: weight matrix [Cout][ldw] (torch's [Cout][Cin][KH][KW] flattened; ldw % 4 == 0, use weight_prep mode 0 to
- * pad). koff / kpos: int32 device tables, one entry per k = (ci,kh,kw), padded to a multiple of 128 entries:
- * koff = ci*H*W + kh*W + kw, kpos = kh | kw << 16, 0x7fff7fff beyond K. TF32 tensor cores, fp32 accumulate.
+ * pad). ktab: device table of int32 pairs, one per k = (ci,kh,kw), padded to a multiple of 128 pairs:
+ * {ci*H*W + kh*W + kw, kh | kw << 16} and {0, 0x7fff7fff} beyond K (k_order 0). k_order 1 = reduction index
+ * ordered (kh,kw,ci) — needs Cin % 32 == 0, no table, weights permuted by weight_prep mode 2 / 3; dw is always
+ * returned in torch's [Cout][Cin][KH][KW] order. TF32 tensor cores (gathered operands rounded), fp32 accumulate.
  * dgrad of a stride-1 convolution = conv2d_fwd on dy with weight_prep mode 1 weights and pad' = KH-1-pad. */
-int b200ddp_conv2d_fwd(const float* x, const float* wmat, long long ldw, const float* bias, float* y, const int* koff,
-                       const int* kpos, int Nb, int Cin, int H, int W, int Cout, int KH, int KW, int stride, int pad,
-                       int relu, int device, void* stream);
+int b200ddp_conv2d_fwd(const float* x, const float* wmat, long long ldw, const float* bias, float* y, const int* ktab,
+                       int k_order, int Nb, int Cin, int H, int W, int Cout, int KH, int KW, int stride, int pad, int relu,
+                       int device, void* stream);
 /* dw [Cout][Cin*KH*KW] = sum over pixels of dy x im2col(x) (written, not accumulated). */
 long long b200ddp_conv2d_wgrad_workspace_bytes(int Nb, int Cin, int H, int W, int Cout, int KH, int KW, int stride,
                                                int pad);
-int b200ddp_conv2d_wgrad(const float* x, const float* dy, float* dw, const int* koff, const int* kpos, int Nb, int Cin,
-                         int H, int W, int Cout, int KH, int KW, int stride, int pad, void* ws, long long ws_bytes,
-                         int device, void* stream);
+int b200ddp_conv2d_wgrad(const float* x, const float* dy, float* dw, const int* ktab, int k_order, int Nb, int Cin, int H,
+                         int W, int Cout, int KH, int KW, int stride, int pad, void* ws, long long ws_bytes, int device,
+                         void* stream);
 /* mode 0: out[co][0..ld_out) = w[co][:] zero padded; mode 1: flipped / transposed weights for dgrad,
- * out[ci][co*KH*KW + (KH-1-kh)*KW + (KW-1-kw)] = w[co][ci][kh][kw], row stride ld_out. */
+ * out[ci][co*KH*KW + (KH-1-kh)*KW + (KW-1-kw)] = w[co][ci][kh][kw], row stride ld_out; modes 2 / 3: the same two
+ * matrices with the reduction index in channel-inner order (k_order 1). */
 int b200ddp_conv2d_weight_prep(const float* w, float* out, int Cout, int Cin, int KH, int KW, long long ld_out, int mode,
                                int device, void* stream);
 /* out[c] = sum over (n, pix) dy[n][c][pix] — the conv bias gradient. scratch: 256-byte aligned, zeroed once. */

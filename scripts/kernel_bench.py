@@ -161,26 +161,21 @@ for (Cin, H, Cout, K, s_, p_, tag) in ((3, 224, 64, 11, 4, 2, "conv1"), (64, 27,
     Kk = Cin * K * K
     fl = 2.0 * B * OH * OH * Cout * Kk
     w = conv.weight.detach()
-    if Kk % 4:
-        ldw = (Kk + 31) // 32 * 32
-        wmat = torch.zeros(Cout, ldw, device=DEV)
-        wmat[:, :Kk] = w.reshape(Cout, Kk)
-    else:
-        ldw, wmat = Kk, w
+    ko = bnn._k_order(Cin)
+    wmat, ldw = bnn.conv_weight_matrix(w, 2 if ko else 0)
     bias = conv.bias.detach()
     yb_ = 4.0 * (xin.numel() + B * Cout * OH * OH + w.numel())
-    timeit(f"conv2d_fwd {tag}", lambda: bnn.conv2d_forward_raw(xin, wmat, ldw, bias, Cout, K, K, s_, p_, False), yb_, fl)
+    timeit(f"conv2d_fwd {tag} (k_order {ko})", lambda: bnn.conv2d_forward_raw(xin, wmat, ldw, bias, Cout, K, K, s_, p_, False, ko), yb_, fl)
     dyc = torch.randn(B, Cout, OH, OH, device=DEV)
     dwc = torch.empty_like(w)
-    koff, kpos = bnn._conv_tables(DEV, Cin, H, H, K, K)
+    ktab = bnn._conv_tables(DEV, Cin, H, H, K, K) if ko == 0 else None
     nb = int(L.b200ddp_conv2d_wgrad_workspace_bytes(B, Cin, H, H, Cout, K, K, s_, p_))
     wsc = torch.empty(max(nb, 256), dtype=torch.uint8, device=DEV)
-    timeit(f"conv2d_wgrad {tag} (incl. split finalize)",
-           lambda: chk(L.b200ddp_conv2d_wgrad(xin.data_ptr(), dyc.data_ptr(), dwc.data_ptr(), koff.data_ptr(), kpos.data_ptr(), B, Cin, H, H,
+    timeit(f"conv2d_wgrad {tag} (k_order {ko}, incl. split finalize)",
+           lambda: chk(L.b200ddp_conv2d_wgrad(xin.data_ptr(), dyc.data_ptr(), dwc.data_ptr(), _lib.ptr(ktab), ko, B, Cin, H, H,
                                               Cout, K, K, s_, p_, wsc.data_ptr(), wsc.numel(), 0, st()), "wgrad"), yb_, fl)
     if s_ == 1:
-        kt = Cout * K * K
-        wt = torch.empty(Cin, kt, device=DEV)
-        chk(L.b200ddp_conv2d_weight_prep(w.data_ptr(), wt.data_ptr(), Cout, Cin, K, K, kt, 1, 0, st()), "prep")
-        timeit(f"conv2d_dgrad {tag}", lambda: bnn.conv2d_forward_raw(dyc, wt, kt, None, Cin, K, K, 1, K - 1 - p_, False), yb_, fl)
+        kod = bnn._k_order(Cout)
+        wt, ldt = bnn.conv_weight_matrix(w, 3 if kod else 1)
+        timeit(f"conv2d_dgrad {tag} (k_order {kod})", lambda: bnn.conv2d_forward_raw(dyc, wt, ldt, None, Cin, K, K, 1, K - 1 - p_, False, kod), yb_, fl)
     del xin, dyc

@@ -107,3 +107,23 @@ def test_weight_prep_and_channel_sum_exact():
         _lib.check(L.b200ddp_channel_sum(dy.data_ptr(), res.data_ptr(), 9, 64, 55 * 55, scratch.data_ptr(),
                                          scratch.numel(), 0, st), "chsum")
         assert torch.allclose(res.double(), dy.double().sum((0, 2, 3)), rtol=1e-5, atol=1e-3)
+
+
+@pytest.mark.parametrize("layer", [1, 2])
+def test_conv_table_order_path_on_wide_layers(layer, monkeypatch):
+    """k_order 0 (torch's (ci,kh,kw) order + offset table) is what conv1 uses; run it on wider layers too."""
+    monkeypatch.setattr(bnn, "_k_order", lambda cin: 0)
+    Cin, H, Cout, K, s, p = LAYERS[layer]
+    torch.manual_seed(layer)
+    x = torch.randn(5, Cin, H, H, device=DEV, requires_grad=True)
+    conv = bnn.Conv2d(Cin, Cout, K, stride=s, padding=p).to(DEV)
+    y = conv(x)
+    dy = torch.randn_like(y)
+    y.backward(dy)
+    x64 = x.detach().double().requires_grad_()
+    w64 = conv.weight.detach().double().requires_grad_()
+    y64 = torch.nn.functional.conv2d(x64, w64, conv.bias.detach().double(), stride=s, padding=p)
+    y64.backward(dy.double())
+    assert _err(y.detach(), y64.detach()) < TOL
+    assert _err(conv.weight.grad, w64.grad) < TOL
+    assert _err(x.grad, x64.grad) < TOL

@@ -57,10 +57,10 @@ _PROTOS = {
     "b200ddp_linear_bwd_dw": (c_int, [_P, _P, _P, _P, c_int, c_int, c_int, c_int, c_int, _P]),
     "b200ddp_gate_bias_bwd": (c_int, [_P, _P, c_float, _P, _P, c_int, c_int, c_int, _P]),
     "b200ddp_softmax_ce": (c_int, [_P, _P, _P, _P, c_int, c_int, _P, c_int, _P]),
-    "b200ddp_conv2d_fwd": (c_int, [_P, _P, c_longlong, _P, _P, _P, _P, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int,
-                                   c_int, c_int, c_int, _P]),
+    "b200ddp_conv2d_fwd": (c_int, [_P, _P, c_longlong, _P, _P, _P, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int,
+                                   c_int, c_int, c_int, c_int, _P]),
     "b200ddp_conv2d_wgrad_workspace_bytes": (c_longlong, [c_int] * 9),
-    "b200ddp_conv2d_wgrad": (c_int, [_P, _P, _P, _P, _P, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int,
+    "b200ddp_conv2d_wgrad": (c_int, [_P, _P, _P, _P, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int,
                                      _P, c_longlong, c_int, _P]),
     "b200ddp_conv2d_weight_prep": (c_int, [_P, _P, c_int, c_int, c_int, c_int, c_longlong, c_int, c_int, _P]),
     "b200ddp_channel_sum_scratch_bytes": (c_longlong, [c_int, c_int]),

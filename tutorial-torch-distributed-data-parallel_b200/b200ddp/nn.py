@@ -146,8 +146,8 @@ _CONV_TABLES: dict = {}
 
 
 def _conv_tables(device, Cin: int, H: int, W: int, KH: int, KW: int):
-    """int32 device tables indexed by k = (ci, kh, kw): input offset and packed window position.
-    Padded to a multiple of 128 entries with an 'invalid' marker (host logic; built once per shape)."""
+    """int32 device table of pairs indexed by k = (ci, kh, kw): {input offset, packed window position}.
+    Padded to a multiple of 128 pairs with an 'invalid' marker (host logic; built once per shape)."""
     key = (str(device), Cin, H, W, KH, KW)
     t = _CONV_TABLES.get(key)
     if t is None:
@@ -160,42 +160,61 @@ def _conv_tables(device, Cin: int, H: int, W: int, KH: int, KW: int):
         kpos = (kh | (kw << 16)).to(torch.int32)
         koff[K:] = 0
         kpos[K:] = 0x7FFF7FFF
-        t = (koff.to(device), kpos.to(device))
+        t = torch.stack([koff, kpos], dim=1).contiguous().to(device)
         _CONV_TABLES[key] = t
     return t
 
 
-def conv2d_forward_raw(x, wmat, ldw, bias, Cout, KH, KW, stride, pad, relu):
-    """y = conv(x, wmat) through b200ddp_conv2d_fwd; x [N,Cin,H,W] contiguous fp32 CUDA."""
+def _k_order(cin: int) -> int:
+    """1 = reduction index ordered (kh, kw, ci) (needs Cin % 32 == 0), 0 = torch's (ci, kh, kw) with a table."""
+    return 1 if cin % 32 == 0 else 0
+
+
+def conv2d_forward_raw(x, wmat, ldw, bias, Cout, KH, KW, stride, pad, relu, k_order):
+    """y = conv(x, wmat) through b200ddp_conv2d_fwd; x [N,Cin,H,W] contiguous fp32 CUDA; wmat in `k_order`."""
     L = _lib.load()
     N, Cin, H, W = x.shape
     OH, OW = (H + 2 * pad - KH) // stride + 1, (W + 2 * pad - KW) // stride + 1
-    koff, kpos = _conv_tables(x.device, Cin, H, W, KH, KW)
+    ktab = _conv_tables(x.device, Cin, H, W, KH, KW) if k_order == 0 else None
     y = torch.empty((N, Cout, OH, OW), dtype=torch.float32, device=x.device)
     _lib.check(L.b200ddp_conv2d_fwd(x.data_ptr(), wmat.data_ptr(), int(ldw), _lib.ptr(bias), y.data_ptr(),
-                                    koff.data_ptr(), kpos.data_ptr(), N, Cin, H, W, Cout, KH, KW, stride, pad,
+                                    _lib.ptr(ktab), k_order, N, Cin, H, W, Cout, KH, KW, stride, pad,
                                     int(bool(relu)), _lib.dev_index(x), _lib.cur_stream(x.device)), "conv2d_fwd")
     return y
+
+
+def conv_weight_matrix(w, mode: int):
+    """Weight matrix for the implicit GEMM (b200ddp_conv2d_weight_prep): mode 0 padded copy / 2 channel-inner
+    forward weights [Cout][K]; 1 / 3 flipped, transposed dgrad weights [Cin][Cout*KH*KW]."""
+    L = _lib.load()
+    Cout, Cin, KH, KW = w.shape
+    if mode in (0, 2):
+        rows, ld = Cout, ((Cin * KH * KW + 31) // 32 * 32 if mode == 0 else Cin * KH * KW)
+    else:
+        rows, ld = Cin, Cout * KH * KW
+    out = torch.empty((rows, ld), dtype=torch.float32, device=w.device)
+    _lib.check(L.b200ddp_conv2d_weight_prep(w.data_ptr(), out.data_ptr(), Cout, Cin, KH, KW, ld, mode,
+                                            _lib.dev_index(w), _lib.cur_stream(w.device)), "weight_prep")
+    return out, ld
 
 
 class _Conv2dFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, weight, bias, stride, pad, relu):
-        L = _lib.load()
         x = _lib.f32c(x, "input")
         w = _lib.f32c(weight, "weight")
         Cout, Cin, KH, KW = w.shape
         if x.shape[1] != Cin:
             raise ValueError(f"Conv2d: input has {x.shape[1]} channels, weight expects {Cin}")
         K = Cin * KH * KW
-        if K % 4 == 0 and w.data_ptr() % 16 == 0:
+        ko = _k_order(Cin)
+        if ko == 1:
+            wmat, ldw = conv_weight_matrix(w, 2)
+        elif K % 4 == 0 and w.data_ptr() % 16 == 0:
             wmat, ldw = w, K
         else:   # TMA needs 16-byte aligned rows: zero-padded copy (conv1: K = 363)
-            ldw = (K + 31) // 32 * 32
-            wmat = torch.empty((Cout, ldw), dtype=torch.float32, device=x.device)
-            _lib.check(L.b200ddp_conv2d_weight_prep(w.data_ptr(), wmat.data_ptr(), Cout, Cin, KH, KW, ldw, 0,
-                                                    _lib.dev_index(x), _lib.cur_stream(x.device)), "weight_prep")
-        y = conv2d_forward_raw(x, wmat, ldw, bias, Cout, KH, KW, stride, pad, relu)
+            wmat, ldw = conv_weight_matrix(w, 0)
+        y = conv2d_forward_raw(x, wmat, ldw, bias, Cout, KH, KW, stride, pad, relu, ko)
         ctx.save_for_backward(x, w, y if relu else None)
         ctx.stride, ctx.pad, ctx.relu = stride, pad, relu
         ctx.weight_param, ctx.bias_param = weight, bias
@@ -226,22 +245,21 @@ class _Conv2dFn(torch.autograd.Function):
         dw = None
         if ctx.needs_input_grad[1]:
             dw = _grad_target(ctx.weight_param, tuple(w.shape), x.device)
-            koff, kpos = _conv_tables(x.device, Cin, H, W, KH, KW)
+            ko = _k_order(Cin)
+            ktab = _conv_tables(x.device, Cin, H, W, KH, KW) if ko == 0 else None
             nb = int(L.b200ddp_conv2d_wgrad_workspace_bytes(N, Cin, H, W, Cout, KH, KW, stride, pad))
             ws = _lib.workspace(x.device, max(nb, 256), "conv_wgrad")
-            _lib.check(L.b200ddp_conv2d_wgrad(x.data_ptr(), dz.data_ptr(), dw.data_ptr(), koff.data_ptr(),
-                                              kpos.data_ptr(), N, Cin, H, W, Cout, KH, KW, stride, pad, ws.data_ptr(),
-                                              ws.numel(), dev, st), "conv2d_wgrad")
+            _lib.check(L.b200ddp_conv2d_wgrad(x.data_ptr(), dz.data_ptr(), dw.data_ptr(), _lib.ptr(ktab), ko, N, Cin, H,
+                                              W, Cout, KH, KW, stride, pad, ws.data_ptr(), ws.numel(), dev, st),
+                       "conv2d_wgrad")
         dx = None
         if ctx.needs_input_grad[0]:
             if stride != 1:
                 raise NotImplementedError("b200ddp Conv2d: input gradients are implemented for stride 1 only "
                                           "(the toy model's strided conv is its first layer)")
-            kt = Cout * KH * KW
-            wt = torch.empty((Cin, kt), dtype=torch.float32, device=x.device)
-            _lib.check(L.b200ddp_conv2d_weight_prep(w.data_ptr(), wt.data_ptr(), Cout, Cin, KH, KW, kt, 1, dev, st),
-                       "weight_prep")
-            dx = conv2d_forward_raw(dz, wt, kt, None, Cin, KH, KW, 1, KH - 1 - pad, False)
+            ko = _k_order(Cout)          # dgrad reduces over (co, kh', kw')
+            wt, ldt = conv_weight_matrix(w, 3 if ko == 1 else 1)
+            dx = conv2d_forward_raw(dz, wt, ldt, None, Cin, KH, KW, 1, KH - 1 - pad, False, ko)
         return dx, dw, db, None, None, None
 
 

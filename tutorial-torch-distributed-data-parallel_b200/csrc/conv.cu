@@ -4,11 +4,11 @@
 // (The reference runs these through cuDNN, also in TF32 — torch's default for convolutions.)
 //
 // No im2col matrix is ever materialised and no NCHW<->NHWC conversion pass runs (the stock path spends
-// ~1 ms per step in cudnn::nchwToNhwcKernel / nhwcToNchwKernel): four producer warps gather the im2col
-// tile of each k-block directly into shared memory in the swizzled layout tcgen05.mma expects, the
-// weight tile arrives by TMA, one thread issues the MMAs, and the same four warps run the epilogue.
+// ~1 ms per step in cudnn::nchwToNhwcKernel / nhwcToNchwKernel): producer warps gather the im2col tile of
+// each k-block directly into shared memory in the swizzled layout tcgen05.mma expects, the weight tile
+// arrives by TMA, one thread issues the MMAs, and the producer warps then run the epilogue.
 //
-//   forward / dgrad   D[m = pixel][n = co] = sum_k  col(pixel, k) * W[co][k]        k = (ci, kh, kw)
+//   forward / dgrad   D[m = pixel][n = co] = sum_k  col(pixel, k) * W[co][k]
 //       A = col tile, MN-major (32 consecutive output pixels are contiguous in smem and — for stride 1 —
 //           in the input row), layout SWIZZLE_128B_BASE32B; B = W rows, K-major, TMA SWIZZLE_128B.
 //       Epilogue: + bias[co], ReLU, coalesced stores y[n][co][pix] (lanes = consecutive pixels).
@@ -18,6 +18,15 @@
 //       both operands K-major (32 consecutive pixels per smem row), gathered by the producer warps;
 //       the pixel range is split over CTAs (deterministic partials + finalize) because only
 //       ceil(K/128) x ceil(Cout/BN) output tiles exist.
+//
+// Two orderings of the reduction index k (the weight matrix is permuted to match by conv_weight_prep):
+//   k_order 0  k = (ci, kh, kw)   torch's own order; per-k offsets come from a small device table. Any Cin.
+//   k_order 1  k = (kh, kw, ci)   "channel inner", needs Cin % 32 == 0: a whole 32-row k-block shares one
+//              (kh, kw), so each producer thread does ONE bounds test per k-block and walks the channels
+//              with a constant stride of H*W — ~6 instructions per gathered element instead of ~20.
+//
+// Producers: kGroups groups of 4 warps; group g fills k-blocks g, g+kGroups, ... with 32 independent
+// loads in flight per thread, rounds to TF32 (round-half-up on the magnitude: one integer add) and stores.
 #include "gemm.h"
 #include "tc.cuh"
 #include "../../include/b200ddp.h"
@@ -31,8 +40,20 @@ using namespace tc;
 constexpr int CBM = 128;            // UMMA_M
 constexpr int CBK = 32;             // fp32 per k-block (128 bytes)
 constexpr int CUK = 8;              // K per tcgen05.mma kind::tf32
-constexpr int kConvThreads = 160;   // warps 0-3: gather producers, then epilogue; warp 4: TMEM + MMA issue
-constexpr int kInvalidPos = 0x7fff7fff;
+constexpr int kGroups = 3;          // forward / dgrad: 3 producer groups x 32 loads in flight per thread
+constexpr int kProdWarps = 4 * kGroups;
+constexpr int kConvThreads = 32 * (kProdWarps + 1);   // producer/epilogue warps + 1 warp: TMEM alloc + MMA issue
+constexpr int kWgGroups = 3;        // wgrad: 3 producer groups, batches of 32 loads software-pipelined in registers
+constexpr int kWgProdWarps = 4 * kWgGroups;
+constexpr int kWgThreads = 32 * (kWgProdWarps + 1);
+
+// fp32 -> tf32 with rounding (half away from zero on the magnitude): the tensor core drops the low 13
+// mantissa bits, so adding half an ulp of tf32 first turns its truncation into rounding.
+__device__ __forceinline__ float round_tf32(float v) { return __uint_as_float(__float_as_uint(v) + 0x1000u); }
+
+__device__ __forceinline__ void sts_f32(uint32_t addr, float v) {
+  asm volatile("st.shared.f32 [%0], %1;" ::"r"(addr), "f"(v) : "memory");
+}
 
 template <int BN>
 constexpr uint32_t tmem_cols() { return BN <= 32 ? 32 : BN <= 64 ? 64 : BN <= 128 ? 128 : 256; }
@@ -41,14 +62,13 @@ struct ConvFwdParams {
   const float* x;
   float* y;
   const float* bias;
-  const int* koff;     // [kblocks*32] ci*H*W + kh*W + kw
-  const int* kpos;     // [kblocks*32] kh | kw << 16 (kInvalidPos beyond K)
-  int Nb, Cin, H, W, Cout, OH, OW, stride, pad;
+  const int2* tab;     // k_order 0: [kblocks*32] {ci*H*W + kh*W + kw, kh | kw << 16 (0x7fff7fff beyond K)}
+  int Nb, Cin, H, W, Cout, OH, OW, KW, stride, pad;
   int kblocks, M, OHW, relu, stages;
 };
 
-template <int BN>
-__global__ void __launch_bounds__(kConvThreads)
+template <int BN, bool CI>
+__global__ void __launch_bounds__(kConvThreads, 1)
 conv_fwd_kernel(const __grid_constant__ CUtensorMap tmW, ConvFwdParams p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -66,66 +86,102 @@ conv_fwd_kernel(const __grid_constant__ CUtensorMap tmW, ConvFwdParams p) {
 
   if (tid == 0) {
     for (int s = 0; s < stages; ++s) {
-      mbar_init(&full_bar[s], 128);     // every producer thread arrives once per phase (+ TMA bytes)
+      mbar_init(&full_bar[s], 128);     // the 128 threads of one producer group arrive once per phase (+ TMA bytes)
       mbar_init(&empty_bar[s], 1);      // tcgen05.commit
     }
     mbar_init(tmem_full_bar, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tmW) : "memory");
   }
-  if (warp == 4) tmem_alloc(tmem_slot, tmem_cols<BN>());
+  if (warp == kProdWarps) tmem_alloc(tmem_slot, tmem_cols<BN>());
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
-  if (warp < 4) {
-    // ---------------- im2col gather producer: thread <-> output pixel ----------------
-    const int m = m0 + tid;
+  if (warp < kProdWarps) {
+    // ---------------- im2col gather producers: thread <-> output pixel, group <-> every kGroups-th k-block ----------------
+    const int group = warp >> 2, gwarp = warp & 3, gtid = tid & 127;
+    const int m = m0 + gtid;
     const bool valid_m = m < p.M;
     const int mm = valid_m ? m : 0;
     const int n_img = mm / p.OHW, pix = mm - n_img * p.OHW;
     const int oh = pix / p.OW, ow = pix - oh * p.OW;
     const int ih0 = oh * p.stride - p.pad, iw0 = ow * p.stride - p.pad;
-    const long long xbase = (long long)n_img * p.Cin * p.H * p.W + (long long)ih0 * p.W + iw0;
+    const long long hw = (long long)p.H * p.W;
+    const float* xb = p.x + ((long long)n_img * p.Cin * hw + (long long)ih0 * p.W + iw0);
     // MN-major SWIZZLE_128B_BASE32B: k-row r at r*128 B, 32-byte chunk c stored at chunk c ^ (r & 3);
-    // the 32-pixel atom `warp` starts at warp*4096 B.
+    // the 32-pixel atom `gwarp` starts at gwarp*4096 B.
     const uint32_t chunk = (uint32_t)lane >> 3;
-    const uint32_t s_thread = (uint32_t)warp * 4096u + ((uint32_t)lane & 7u) * 4u;
-    for (int kb = 0; kb < p.kblocks; ++kb) {
+    const uint32_t s_thread = (uint32_t)gwarp * 4096u + ((uint32_t)lane & 7u) * 4u;
+    uint32_t s_chunk[4];
+#pragma unroll
+    for (int c = 0; c < 4; ++c) s_chunk[c] = s_thread + ((chunk ^ (uint32_t)c) << 5);
+    const int cb = CI ? (p.Cin >> 5) : 1;      // channel blocks per (kh, kw)
+    // Software pipeline in registers: the 32 loads of this group's NEXT k-block are issued before the current
+    // one is stored, and before its smem slot is even free — loads never wait for the MMA, stores never wait
+    // for DRAM/L2 (the data arrived while the previous block was being stored).
+    auto issue = [&](int kb, float (&v)[CBK]) {
+      if (CI) {
+        const int khkw = kb / cb, ci0 = (kb - khkw * cb) << 5;
+        const int kh = khkw / p.KW, kw = khkw - kh * p.KW;
+        const bool ok = valid_m && (unsigned)(ih0 + kh) < (unsigned)p.H && (unsigned)(iw0 + kw) < (unsigned)p.W;
+        const float* q = xb + ((long long)ci0 * hw + kh * p.W + kw);
+#pragma unroll
+        for (int r = 0; r < CBK; ++r) {       // constant stride H*W between channels
+          v[r] = 0.f;
+          if (ok) v[r] = __ldg(q);
+          q += hw;
+        }
+      } else {
+        const int2* tab = p.tab + kb * CBK;
+#pragma unroll
+        for (int r = 0; r < CBK; ++r) {
+          const int2 t = __ldg(tab + r);      // uniform address: one broadcast transaction per warp
+          const int ih = ih0 + (t.y & 0xffff), iw = iw0 + (t.y >> 16);
+          const bool ok = valid_m && (unsigned)ih < (unsigned)p.H && (unsigned)iw < (unsigned)p.W;
+          v[r] = 0.f;
+          if (ok) v[r] = __ldg(xb + t.x);
+        }
+      }
+    };
+    auto commit = [&](int kb, const float (&v)[CBK]) {
       const int s = kb % stages;
       const uint32_t ph = (uint32_t)(kb / stages) & 1u;
       mbar_wait(&empty_bar[s], ph ^ 1u);
       uint8_t* sa = smem + (size_t)s * STAGE_BYTES;
-      if (tid == 0) {
+      if (gtid == 0) {
         mbar_expect_tx(&full_bar[s], B_BYTES);
         tma_load_2d(sa + A_BYTES, &tmW, &full_bar[s], kb * CBK, n0);       // box {32 k, BN co}
       }
-      const int my_off = __ldg(p.koff + kb * CBK + lane);
-      const int my_pos = __ldg(p.kpos + kb * CBK + lane);
-      const uint32_t sdst = smem_u32(sa) + s_thread;
-#pragma unroll 8
-      for (int r = 0; r < CBK; ++r) {
-        const int off = __shfl_sync(0xffffffffu, my_off, r);
-        const int pos = __shfl_sync(0xffffffffu, my_pos, r);
-        const int ih = ih0 + (pos & 0xffff), iw = iw0 + (pos >> 16);
-        const bool ok = valid_m && (unsigned)ih < (unsigned)p.H && (unsigned)iw < (unsigned)p.W;
-        float v = 0.f;
-        if (ok) v = __ldg(p.x + xbase + off);
-        const uint32_t addr = sdst + (uint32_t)r * 128u + ((chunk ^ ((uint32_t)r & 3u)) << 5);
-        asm volatile("st.shared.f32 [%0], %1;" ::"r"(addr), "f"(v) : "memory");
-      }
+      const uint32_t sdst = smem_u32(sa);
+#pragma unroll
+      for (int r = 0; r < CBK; ++r) sts_f32(sdst + s_chunk[r & 3] + (uint32_t)r * 128u, round_tf32(v[r]));
       fence_proxy_async_smem();
       mbar_arrive(&full_bar[s]);
+    };
+    {
+      float va[CBK], vb[CBK];
+      int kb = group;
+      if (kb < p.kblocks) issue(kb, va);
+      while (kb < p.kblocks) {
+        const int kb2 = kb + kGroups;
+        if (kb2 < p.kblocks) issue(kb2, vb);
+        commit(kb, va);
+        if (kb2 >= p.kblocks) break;
+        kb = kb2 + kGroups;
+        if (kb < p.kblocks) issue(kb, va);
+        commit(kb2, vb);
+      }
     }
-    // ---------------- epilogue: TMEM lane = pixel, columns = output channels ----------------
+    // ---------------- epilogue: TMEM lane = pixel, columns = output channels; 32-column chunks round-robin over groups ----------------
     mbar_wait(tmem_full_bar, 0);
     tc_fence_after();
     float* yb = p.y + (long long)n_img * p.Cout * p.OHW + pix;
 #pragma unroll 1
-    for (int c = 0; c < BN; c += 32) {
+    for (int c = group * 32; c < BN; c += 32 * kGroups) {
       uint32_t r[32];
-      tmem_ld_32x32(tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)c, r);
+      tmem_ld_32x32(tmem_base + ((uint32_t)(gwarp * 32) << 16) + (uint32_t)c, r);
       if (valid_m) {
 #pragma unroll
         for (int j = 0; j < 32; ++j) {
@@ -162,21 +218,21 @@ conv_fwd_kernel(const __grid_constant__ CUtensorMap tmW, ConvFwdParams p) {
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 4) tmem_dealloc(tmem_base, tmem_cols<BN>());
+  if (warp == kProdWarps) tmem_dealloc(tmem_base, tmem_cols<BN>());
 }
 
 struct ConvWgradParams {
   const float* x;
   const float* dy;
-  float* out;          // dW [Cout][K] (splits == 1) or partials [z][Cout][K]
-  const int* koff;     // [m_tiles*128]
-  const int* kpos;
-  int Nb, Cin, H, W, Cout, OH, OW, stride, pad;
+  float* out;          // gradient matrix [Cout][K] in GEMM k order (splits == 1, k_order 0) or partials [z][Cout][K]
+  float* dw_direct;    // k_order 1 and splits == 1: dW in torch order, written with the permuted index
+  const int2* tab;     // k_order 0: [m_tiles*128] {input offset, kh | kw << 16}
+  int Nb, Cin, H, W, Cout, OH, OW, KH, KW, stride, pad;
   int K, M, OHW, kblocks_total, kblocks_per_split, splits, stages;
 };
 
-template <int BN>
-__global__ void __launch_bounds__(kConvThreads)
+template <int BN, bool CI>
+__global__ void __launch_bounds__(kWgThreads, 1)
 conv_wgrad_kernel(ConvWgradParams p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -188,8 +244,7 @@ conv_wgrad_kernel(ConvWgradParams p) {
   uint64_t* empty_bar = full_bar + stages;
   uint64_t* tmem_full_bar = empty_bar + stages;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full_bar + 1);
-  int* s_koff = reinterpret_cast<int*>(tmem_slot + 4);
-  int* s_kpos = s_koff + CBM;
+  int2* s_tab = reinterpret_cast<int2*>(tmem_slot + 4);
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int m0 = blockIdx.x * CBM, n0 = blockIdx.y * BN, z = blockIdx.z;
@@ -198,10 +253,7 @@ conv_wgrad_kernel(ConvWgradParams p) {
   if (kb_end > p.kblocks_total) kb_end = p.kblocks_total;
   const int nkb = kb_end - kb_begin;
 
-  if (tid < CBM) {
-    s_koff[tid] = __ldg(p.koff + m0 + tid);
-    s_kpos[tid] = __ldg(p.kpos + m0 + tid);
-  }
+  if (!CI && tid < CBM) s_tab[tid] = __ldg(p.tab + m0 + tid);
   if (tid == 0) {
     for (int s = 0; s < stages; ++s) {
       mbar_init(&full_bar[s], 128);
@@ -210,68 +262,139 @@ conv_wgrad_kernel(ConvWgradParams p) {
     mbar_init(tmem_full_bar, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
-  if (warp == 4) tmem_alloc(tmem_slot, tmem_cols<BN>());
+  if (warp == kWgProdWarps) tmem_alloc(tmem_slot, tmem_cols<BN>());
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
-  if (warp < 4) {
-    // ---------------- producers: lane <-> pixel of the k-block, warp <-> quarter of the tile rows ----------------
+  if (warp < kWgProdWarps) {
+    // ---------------- producers: lane <-> pixel of the k-block, warp <-> quarter of the tile rows,
+    //                  group <-> every kWgGroups-th k-block ----------------
+    const int group = warp >> 2, gwarp = warp & 3;
     constexpr int B_ROWS = BN / 4;
+    const long long hw = (long long)p.H * p.W;
     // K-major SWIZZLE_128B: row i at i*128 B, 16-byte chunk c stored at chunk c ^ (i & 7)
     const uint32_t c16 = (uint32_t)lane >> 2, e16 = ((uint32_t)lane & 3u) * 4u;
-    for (int i = 0; i < nkb; ++i) {
-      const int s = i % stages;
-      const uint32_t ph = (uint32_t)(i / stages) & 1u;
-      mbar_wait(&empty_bar[s], ph ^ 1u);
+    uint32_t s_chunk[8];
+#pragma unroll
+    for (int c = 0; c < 8; ++c) s_chunk[c] = ((c16 ^ (uint32_t)c) << 4) + e16;
+    // channel-inner order: the warp's 32 rows k0..k0+31 share one (kh, kw) and cover channels ci0..ci0+31
+    const int k0 = m0 + gwarp * 32;
+    const bool rows_valid = k0 < p.K;
+    const int khkw_w = CI ? (rows_valid ? k0 / p.Cin : 0) : 0;
+    const int ci0_w = CI ? (rows_valid ? k0 - khkw_w * p.Cin : 0) : 0;
+    const int kh_w = khkw_w / p.KW, kw_w = khkw_w - kh_w * p.KW;
+    // Work of one k-block for a thread = batches of <= 32 loads: [A rows] [B rows 0..31] [B rows 32..].
+    // Software pipeline in registers: the loads of the NEXT batch are issued before the current batch is stored
+    // (and before the current k-block's smem slot is known to be free), so a batch of loads is always in flight.
+    constexpr int NB = 1 + (B_ROWS + 31) / 32;
+    int li = group, lt = 0;            // load cursor: (k-block, batch)
+    int si = group, st_ = 0;           // store cursor
+    bool l_valid = false, l_okA = false;
+    const float* l_xq = p.x;
+    const float* l_dyb = p.dy;
+    auto load = [&](float (&v)[32]) {
+      if (lt == 0) {
+        const int pxl = (kb_begin + li) * CBK + lane;
+        l_valid = pxl < p.M;
+        const int pp = l_valid ? pxl : 0;
+        const int n_img = pp / p.OHW, pix = pp - n_img * p.OHW;
+        const int oh = pix / p.OW, ow = pix - oh * p.OW;
+        const int ih0 = oh * p.stride - p.pad, iw0 = ow * p.stride - p.pad;
+        const float* xb = p.x + ((long long)n_img * p.Cin * hw + (long long)ih0 * p.W + iw0);
+        l_dyb = p.dy + (long long)n_img * p.Cout * p.OHW + pix;
+        if (CI) {
+          l_okA = l_valid && rows_valid && (unsigned)(ih0 + kh_w) < (unsigned)p.H && (unsigned)(iw0 + kw_w) < (unsigned)p.W;
+          const float* q = xb + ((long long)ci0_w * hw + kh_w * p.W + kw_w);
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            v[j] = 0.f;
+            if (l_okA) v[j] = __ldg(q);
+            q += hw;
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            const int2 t = s_tab[gwarp * 32 + j];
+            const int ih = ih0 + (t.y & 0xffff), iw = iw0 + (t.y >> 16);
+            const bool ok = l_valid && (unsigned)ih < (unsigned)p.H && (unsigned)iw < (unsigned)p.W;
+            v[j] = 0.f;
+            if (ok) v[j] = __ldg(xb + t.x);
+          }
+        }
+      } else {
+        const int r0 = (lt - 1) * 32;
+        const int co0 = n0 + gwarp * B_ROWS + r0;
+        const float* q = l_dyb + (long long)co0 * p.OHW;
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+          v[j] = 0.f;
+          if (r0 + j < B_ROWS && l_valid && co0 + j < p.Cout) v[j] = __ldg(q);
+          q += p.OHW;
+        }
+      }
+      if (++lt == NB) { lt = 0; li += kWgGroups; }
+    };
+    auto store = [&](const float (&v)[32]) {
+      const int s = si % stages;
       const uint32_t sa = smem_u32(smem + (size_t)s * STAGE_BYTES);
-      const uint32_t sb = sa + A_BYTES;
-      const int pxl = (kb_begin + i) * CBK + lane;
-      const bool valid_p = pxl < p.M;
-      const int pp = valid_p ? pxl : 0;
-      const int n_img = pp / p.OHW, pix = pp - n_img * p.OHW;
-      const int oh = pix / p.OW, ow = pix - oh * p.OW;
-      const int ih0 = oh * p.stride - p.pad, iw0 = ow * p.stride - p.pad;
-      const long long xbase = (long long)n_img * p.Cin * p.H * p.W + (long long)ih0 * p.W + iw0;
-      const float* dyb = p.dy + (long long)n_img * p.Cout * p.OHW + pix;
-#pragma unroll 8
-      for (int j = 0; j < 32; ++j) {
-        const int row = warp * 32 + j;
-        const int off = s_koff[row], pos = s_kpos[row];
-        const int ih = ih0 + (pos & 0xffff), iw = iw0 + (pos >> 16);
-        const bool ok = valid_p && (unsigned)ih < (unsigned)p.H && (unsigned)iw < (unsigned)p.W;
-        float v = 0.f;
-        if (ok) v = __ldg(p.x + xbase + off);
-        const uint32_t addr = sa + (uint32_t)row * 128u + ((c16 ^ ((uint32_t)row & 7u)) << 4) + e16;
-        asm volatile("st.shared.f32 [%0], %1;" ::"r"(addr), "f"(v) : "memory");
+      if (st_ == 0) {
+        mbar_wait(&empty_bar[s], ((uint32_t)(si / stages) & 1u) ^ 1u);
+#pragma unroll
+        for (int j = 0; j < 32; ++j)      // (gwarp*32 + j) & 7 == j & 7
+          sts_f32(sa + (uint32_t)(gwarp * 32 + j) * 128u + s_chunk[j & 7], round_tf32(v[j]));
+      } else {
+        const int r0 = (st_ - 1) * 32;
+        const uint32_t sb = sa + A_BYTES;
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+          const int row = gwarp * B_ROWS + r0 + j;      // B_ROWS and r0 are multiples of 8 -> row & 7 == j & 7
+          if (r0 + j < B_ROWS) sts_f32(sb + (uint32_t)row * 128u + s_chunk[j & 7], round_tf32(v[j]));
+        }
       }
-#pragma unroll 8
-      for (int j = 0; j < B_ROWS; ++j) {
-        const int row = warp * B_ROWS + j;
-        const int co = n0 + row;
-        float v = 0.f;
-        if (valid_p && co < p.Cout) v = __ldg(dyb + (long long)co * p.OHW);
-        const uint32_t addr = sb + (uint32_t)row * 128u + ((c16 ^ ((uint32_t)row & 7u)) << 4) + e16;
-        asm volatile("st.shared.f32 [%0], %1;" ::"r"(addr), "f"(v) : "memory");
+      if (++st_ == NB) {
+        fence_proxy_async_smem();
+        mbar_arrive(&full_bar[s]);
+        st_ = 0;
+        si += kWgGroups;
       }
-      fence_proxy_async_smem();
-      mbar_arrive(&full_bar[s]);
+    };
+    {
+      float ra[32], rb[32];
+      if (li < nkb) load(ra);
+      while (si < nkb) {
+        if (li < nkb) load(rb);
+        store(ra);
+        if (si >= nkb) break;
+        if (li < nkb) load(ra);
+        store(rb);
+      }
     }
     // ---------------- epilogue: TMEM lane = k index, columns = output channels ----------------
     mbar_wait(tmem_full_bar, 0);
     tc_fence_after();
-    const int m = m0 + tid;
-    float* ob = p.out + (long long)z * p.Cout * p.K + m;
+    const int m = m0 + gwarp * 32 + lane;
+    float* ob;
+    long long ld;
+    if (CI && p.splits == 1) {       // un-permute (kh,kw,ci) -> torch's (ci,kh,kw) while storing
+      const int khkw = m < p.K ? m / p.Cin : 0;
+      const int ci = m - khkw * p.Cin;
+      ob = p.dw_direct + (long long)ci * (p.KH * p.KW) + khkw;
+      ld = p.K;
+    } else {
+      ob = p.out + (long long)z * p.Cout * p.K + m;
+      ld = p.K;
+    }
 #pragma unroll 1
-    for (int c = 0; c < BN; c += 32) {
+    for (int c = group * 32; c < BN; c += 32 * kWgGroups) {
       uint32_t r[32];
-      tmem_ld_32x32(tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)c, r);
+      tmem_ld_32x32(tmem_base + ((uint32_t)(gwarp * 32) << 16) + (uint32_t)c, r);
       if (m < p.K) {
 #pragma unroll
         for (int j = 0; j < 32; ++j) {
           const int co = n0 + c + j;
-          if (co < p.Cout) ob[(long long)co * p.K] = __uint_as_float(r[j]);
+          if (co < p.Cout) ob[(long long)co * ld] = __uint_as_float(r[j]);
         }
       }
     }
@@ -296,11 +419,27 @@ conv_wgrad_kernel(ConvWgradParams p) {
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 4) tmem_dealloc(tmem_base, tmem_cols<BN>());
+  if (warp == kWgProdWarps) tmem_dealloc(tmem_base, tmem_cols<BN>());
+}
+
+// dW[co][ci][kh][kw] = sum_z ws[z][co][(kh*KW + kw)*Cin + ci]   (k_order 1 partials -> torch order)
+__global__ void __launch_bounds__(256) wgrad_finalize_ci_kernel(const float* __restrict__ ws, int splits, int Cout, int Cin,
+                                                                int KHW, float* __restrict__ dw) {
+  const long long K = (long long)Cin * KHW, total = (long long)Cout * K, stride = (long long)gridDim.x * blockDim.x;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
+    // i enumerates the GEMM order (coalesced reads): co, khkw, ci
+    const long long co = i / K, k = i - co * K;
+    const int khkw = (int)(k / Cin), ci = (int)(k - (long long)khkw * Cin);
+    float s = 0.f;
+    for (int z = 0; z < splits; ++z) s += __ldg(ws + (long long)z * total + i);
+    dw[co * K + (long long)ci * KHW + khkw] = s;
+  }
 }
 
 // mode 0: out[co][k] = w[co][k] for k < K, zero padding up to ld_out (row stride multiple of 4 for TMA)
-// mode 1: dgrad weights  out[ci][co*KH*KW + (KH-1-kh)*KW + (KW-1-kw)] = w[co][ci][kh][kw]
+// mode 1: dgrad weights, k' = (co, kh', kw'):  out[ci][co*KH*KW + (KH-1-kh)*KW + (KW-1-kw)] = w[co][ci][kh][kw]
+// mode 2: forward weights in channel-inner order:  out[co][(kh*KW + kw)*Cin + ci]             = w[co][ci][kh][kw]
+// mode 3: dgrad weights in channel-inner order:    out[ci][((KH-1-kh)*KW + (KW-1-kw))*Cout + co] = w[co][ci][kh][kw]
 __global__ void __launch_bounds__(256) conv_weight_prep_kernel(const float* __restrict__ w, float* __restrict__ out,
                                                                int Cout, int Cin, int KH, int KW, long long ld_out,
                                                                int mode) {
@@ -311,6 +450,19 @@ __global__ void __launch_bounds__(256) conv_weight_prep_kernel(const float* __re
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
       const int co = (int)(i / ld_out), k = (int)(i - (long long)co * ld_out);
       out[i] = k < K ? __ldg(w + (long long)co * K + k) : 0.f;
+    }
+  } else if (mode == 2 || mode == 3) {
+    const long long total = (long long)Cout * Cin * KHW, stride = (long long)gridDim.x * blockDim.x;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
+      // i enumerates the INPUT w[co][ci][kh][kw]
+      const int kw = (int)(i % KW);
+      long long t = i / KW;
+      const int kh = (int)(t % KH);
+      t /= KH;
+      const int ci = (int)(t % Cin), co = (int)(t / Cin);
+      const float v = __ldg(w + i);
+      if (mode == 2) out[(long long)co * ld_out + (long long)(kh * KW + kw) * Cin + ci] = v;
+      else out[(long long)ci * ld_out + (long long)((KH - 1 - kh) * KW + (KW - 1 - kw)) * Cout + co] = v;
     }
   } else {
     const long long total = (long long)Cout * Cin * KHW, stride = (long long)gridDim.x * blockDim.x;
@@ -365,13 +517,13 @@ inline int cs_splits(int Nb, int C) {
   return s < 1 ? 1 : s;
 }
 
-template <int BN>
+template <int BN, bool CI>
 int launch_fwd(const CUtensorMap& tmW, const ConvFwdParams& p, cudaStream_t stream) {
   const size_t stage_bytes = (size_t)(CBM + BN) * CBK * 4;
   const size_t smem = 1024 + (size_t)p.stages * stage_bytes + (2 * p.stages + 1) * 8 + 16;
   static bool attr_set = false;
   if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(conv_fwd_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    cudaError_t e = cudaFuncSetAttribute(conv_fwd_kernel<BN, CI>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
     if (e != cudaSuccess) {
       set_error("cudaFuncSetAttribute(conv_fwd_kernel<%d>) -> %s", BN, cudaGetErrorString(e));
       return kCudaErrBase + (int)e;
@@ -379,7 +531,7 @@ int launch_fwd(const CUtensorMap& tmW, const ConvFwdParams& p, cudaStream_t stre
     attr_set = true;
   }
   dim3 grid((p.M + CBM - 1) / CBM, (p.Cout + BN - 1) / BN, 1);
-  conv_fwd_kernel<BN><<<grid, kConvThreads, smem, stream>>>(tmW, p);
+  conv_fwd_kernel<BN, CI><<<grid, kConvThreads, smem, stream>>>(tmW, p);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) {
     set_error("conv_fwd_kernel<%d> launch (grid %d,%d smem %zu) -> %s", BN, grid.x, grid.y, smem, cudaGetErrorString(e));
@@ -389,13 +541,13 @@ int launch_fwd(const CUtensorMap& tmW, const ConvFwdParams& p, cudaStream_t stre
   return 0;
 }
 
-template <int BN>
+template <int BN, bool CI>
 int launch_wgrad(const ConvWgradParams& p, cudaStream_t stream) {
   const size_t stage_bytes = (size_t)(CBM + BN) * CBK * 4;
-  const size_t smem = 1024 + (size_t)p.stages * stage_bytes + (2 * p.stages + 1) * 8 + 32 + 2 * CBM * 4;
+  const size_t smem = 1024 + (size_t)p.stages * stage_bytes + (2 * p.stages + 1) * 8 + 32 + CBM * 8;
   static bool attr_set = false;
   if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(conv_wgrad_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    cudaError_t e = cudaFuncSetAttribute(conv_wgrad_kernel<BN, CI>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
     if (e != cudaSuccess) {
       set_error("cudaFuncSetAttribute(conv_wgrad_kernel<%d>) -> %s", BN, cudaGetErrorString(e));
       return kCudaErrBase + (int)e;
@@ -403,7 +555,7 @@ int launch_wgrad(const ConvWgradParams& p, cudaStream_t stream) {
     attr_set = true;
   }
   dim3 grid((p.K + CBM - 1) / CBM, (p.Cout + BN - 1) / BN, p.splits);
-  conv_wgrad_kernel<BN><<<grid, kConvThreads, smem, stream>>>(p);
+  conv_wgrad_kernel<BN, CI><<<grid, kWgThreads, smem, stream>>>(p);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) {
     set_error("conv_wgrad_kernel<%d> launch (grid %d,%d,%d smem %zu) -> %s", BN, grid.x, grid.y, grid.z, smem,
@@ -453,10 +605,13 @@ using namespace b200;
 
 extern "C" {
 
-int b200ddp_conv2d_fwd(const float* x, const float* wmat, long long ldw, const float* bias, float* y, const int* koff,
-                       const int* kpos, int Nb, int Cin, int H, int W, int Cout, int KH, int KW, int stride, int pad,
-                       int relu, int device, void* stream) {
-  B200_CHECK_ARG(x && wmat && y && koff && kpos, "conv2d_fwd: null argument");
+int b200ddp_conv2d_fwd(const float* x, const float* wmat, long long ldw, const float* bias, float* y, const int* ktab,
+                       int k_order, int Nb, int Cin, int H, int W, int Cout, int KH, int KW, int stride, int pad, int relu,
+                       int device, void* stream) {
+  B200_CHECK_ARG(x && wmat && y, "conv2d_fwd: null argument");
+  B200_CHECK_ARG(k_order == 0 || k_order == 1, "conv2d_fwd: k_order must be 0 (ci,kh,kw) or 1 (kh,kw,ci)");
+  B200_CHECK_ARG(k_order == 1 || (ktab && ((uintptr_t)ktab & 7) == 0), "conv2d_fwd: k_order 0 needs an 8-byte aligned ktab");
+  B200_CHECK_ARG(k_order == 0 || (Cin % 32) == 0, "conv2d_fwd: k_order 1 needs Cin %% 32 == 0 (Cin = %d)", Cin);
   B200_CHECK_ARG(Nb > 0 && Cin > 0 && Cout > 0 && KH > 0 && KW > 0 && stride > 0 && pad >= 0, "conv2d_fwd: bad shape");
   B200_CHECK_ARG((ldw & 3) == 0 && ((uintptr_t)wmat & 15) == 0, "conv2d_fwd: weight rows must be 16-byte aligned (ldw %% 4 == 0)");
   const int OH = (H + 2 * pad - KH) / stride + 1, OW = (W + 2 * pad - KW) / stride + 1;
@@ -465,26 +620,34 @@ int b200ddp_conv2d_fwd(const float* x, const float* wmat, long long ldw, const f
   B200_DEVICE(device);
   const int K = Cin * KH * KW;
   ConvFwdParams p;
-  p.x = x; p.y = y; p.bias = bias; p.koff = koff; p.kpos = kpos;
-  p.Nb = Nb; p.Cin = Cin; p.H = H; p.W = W; p.Cout = Cout; p.OH = OH; p.OW = OW; p.stride = stride; p.pad = pad;
+  p.x = x; p.y = y; p.bias = bias; p.tab = reinterpret_cast<const int2*>(ktab);
+  p.Nb = Nb; p.Cin = Cin; p.H = H; p.W = W; p.Cout = Cout; p.OH = OH; p.OW = OW; p.KW = KW; p.stride = stride; p.pad = pad;
   p.kblocks = (K + CBK - 1) / CBK;
   p.M = Nb * OH * OW; p.OHW = OH * OW; p.relu = relu;
   const int bn = pick_bn(Cout);
   const size_t stage_bytes = (size_t)(CBM + bn) * CBK * 4;
   int stages = (int)((200 * 1024) / stage_bytes);
-  if (stages > 6) stages = 6;
+  if (stages > 8) stages = 8;
   if (stages > p.kblocks) stages = p.kblocks;
-  if (stages < 2) stages = 2;
+  if (stages < kGroups) stages = kGroups;
   p.stages = stages;
   CUtensorMap tmW;
   int rc = tma_map_2d(&tmW, wmat, ldw, Cout, ldw, CBK, bn, 0);
   if (rc) return rc;
   cudaStream_t s = as_stream(stream);
+  if (k_order == 1) {
+    switch (bn) {
+      case 64: return launch_fwd<64, true>(tmW, p, s);
+      case 128: return launch_fwd<128, true>(tmW, p, s);
+      case 192: return launch_fwd<192, true>(tmW, p, s);
+      default: return launch_fwd<256, true>(tmW, p, s);
+    }
+  }
   switch (bn) {
-    case 64: return launch_fwd<64>(tmW, p, s);
-    case 128: return launch_fwd<128>(tmW, p, s);
-    case 192: return launch_fwd<192>(tmW, p, s);
-    default: return launch_fwd<256>(tmW, p, s);
+    case 64: return launch_fwd<64, false>(tmW, p, s);
+    case 128: return launch_fwd<128, false>(tmW, p, s);
+    case 192: return launch_fwd<192, false>(tmW, p, s);
+    default: return launch_fwd<256, false>(tmW, p, s);
   }
 }
 
@@ -495,10 +658,13 @@ long long b200ddp_conv2d_wgrad_workspace_bytes(int Nb, int Cin, int H, int W, in
   return w.splits > 1 ? (long long)w.splits * Cout * Cin * KH * KW * 4 : 0;
 }
 
-int b200ddp_conv2d_wgrad(const float* x, const float* dy, float* dw, const int* koff, const int* kpos, int Nb, int Cin,
-                         int H, int W, int Cout, int KH, int KW, int stride, int pad, void* ws, long long ws_bytes,
-                         int device, void* stream) {
-  B200_CHECK_ARG(x && dy && dw && koff && kpos, "conv2d_wgrad: null argument");
+int b200ddp_conv2d_wgrad(const float* x, const float* dy, float* dw, const int* ktab, int k_order, int Nb, int Cin, int H,
+                         int W, int Cout, int KH, int KW, int stride, int pad, void* ws, long long ws_bytes, int device,
+                         void* stream) {
+  B200_CHECK_ARG(x && dy && dw, "conv2d_wgrad: null argument");
+  B200_CHECK_ARG(k_order == 0 || k_order == 1, "conv2d_wgrad: k_order must be 0 or 1");
+  B200_CHECK_ARG(k_order == 1 || (ktab && ((uintptr_t)ktab & 7) == 0), "conv2d_wgrad: k_order 0 needs an 8-byte aligned ktab");
+  B200_CHECK_ARG(k_order == 0 || (Cin % 32) == 0, "conv2d_wgrad: k_order 1 needs Cin %% 32 == 0 (Cin = %d)", Cin);
   const int OH = (H + 2 * pad - KH) / stride + 1, OW = (W + 2 * pad - KW) / stride + 1;
   B200_CHECK_ARG(OH > 0 && OW > 0 && Nb > 0, "conv2d_wgrad: bad shape");
   B200_CHECK_ARG((long long)Nb * OH * OW < (1ll << 31) && (long long)Cin * H * W < (1ll << 31), "conv2d_wgrad: tensor too large");
@@ -507,27 +673,46 @@ int b200ddp_conv2d_wgrad(const float* x, const float* dy, float* dw, const int* 
   const int K = Cin * KH * KW;
   B200_CHECK_ARG(w.splits == 1 || (ws && ws_bytes >= (long long)w.splits * Cout * K * 4), "conv2d_wgrad: workspace too small");
   ConvWgradParams p;
-  p.x = x; p.dy = dy; p.koff = koff; p.kpos = kpos;
+  p.x = x; p.dy = dy; p.tab = reinterpret_cast<const int2*>(ktab);
   p.out = w.splits > 1 ? reinterpret_cast<float*>(ws) : dw;
-  p.Nb = Nb; p.Cin = Cin; p.H = H; p.W = W; p.Cout = Cout; p.OH = OH; p.OW = OW; p.stride = stride; p.pad = pad;
+  p.dw_direct = dw;
+  p.Nb = Nb; p.Cin = Cin; p.H = H; p.W = W; p.Cout = Cout; p.OH = OH; p.OW = OW; p.KH = KH; p.KW = KW;
+  p.stride = stride; p.pad = pad;
   p.K = K; p.M = Nb * OH * OW; p.OHW = OH * OW;
   p.kblocks_total = w.kblocks_total; p.kblocks_per_split = w.per; p.splits = w.splits;
   const size_t stage_bytes = (size_t)(CBM + w.bn) * CBK * 4;
   int stages = (int)((200 * 1024) / stage_bytes);
-  if (stages > 4) stages = 4;
+  if (stages > 6) stages = 6;
   if (stages > w.per) stages = w.per;
-  if (stages < 2) stages = 2;
+  if (stages < kWgGroups) stages = kWgGroups;
   p.stages = stages;
   cudaStream_t s = as_stream(stream);
   int rc;
-  switch (w.bn) {
-    case 64: rc = launch_wgrad<64>(p, s); break;
-    case 128: rc = launch_wgrad<128>(p, s); break;
-    case 192: rc = launch_wgrad<192>(p, s); break;
-    default: rc = launch_wgrad<256>(p, s); break;
+  if (k_order == 1) {
+    switch (w.bn) {
+      case 64: rc = launch_wgrad<64, true>(p, s); break;
+      case 128: rc = launch_wgrad<128, true>(p, s); break;
+      case 192: rc = launch_wgrad<192, true>(p, s); break;
+      default: rc = launch_wgrad<256, true>(p, s); break;
+    }
+  } else {
+    switch (w.bn) {
+      case 64: rc = launch_wgrad<64, false>(p, s); break;
+      case 128: rc = launch_wgrad<128, false>(p, s); break;
+      case 192: rc = launch_wgrad<192, false>(p, s); break;
+      default: rc = launch_wgrad<256, false>(p, s); break;
+    }
   }
   if (rc) return rc;
   if (w.splits > 1) {
+    if (k_order == 1) {
+      const long long total = (long long)Cout * K;
+      long long want = (total + 255) / 256;
+      const int grid = (int)(want < kNumSMs * 8 ? want : kNumSMs * 8);
+      wgrad_finalize_ci_kernel<<<grid, 256, 0, s>>>(reinterpret_cast<const float*>(ws), w.splits, Cout, Cin, KH * KW, dw);
+      B200_LAUNCH_OK();
+      return 0;
+    }
     Epilogue ep;
     return splitk_finalize_launch(reinterpret_cast<const float*>(ws), w.splits, Cout, K, dw, K, ep, s);
   }
@@ -537,7 +722,8 @@ int b200ddp_conv2d_wgrad(const float* x, const float* dy, float* dw, const int* 
 int b200ddp_conv2d_weight_prep(const float* w, float* out, int Cout, int Cin, int KH, int KW, long long ld_out, int mode,
                                int device, void* stream) {
   B200_CHECK_ARG(w && out && Cout > 0 && Cin > 0 && KH > 0 && KW > 0, "conv2d_weight_prep: bad argument");
-  B200_CHECK_ARG(mode == 0 ? ld_out >= (long long)Cin * KH * KW : ld_out >= (long long)Cout * KH * KW,
+  B200_CHECK_ARG(mode >= 0 && mode <= 3, "conv2d_weight_prep: mode must be 0..3");
+  B200_CHECK_ARG((mode == 0 || mode == 2) ? ld_out >= (long long)Cin * KH * KW : ld_out >= (long long)Cout * KH * KW,
                  "conv2d_weight_prep: ld_out too small");
   B200_DEVICE(device);
   const long long total = mode == 0 ? (long long)Cout * ld_out : (long long)Cout * Cin * KH * KW;
