@@ -141,6 +141,15 @@ long long b200ddp_channel_sum_scratch_bytes(int Nb, int C);
 int b200ddp_channel_sum(const float* dy, float* out, int Nb, int C, int HW, void* scratch, long long scratch_bytes,
                         int device, void* stream);
 
+/* Same result as b200ddp_channel_sum, for callers that cannot hand in scratch memory (no allocator within reach,
+ * or cudaMalloc forbidden on their path). No counterpart in the reference: this exists only because of the
+ * library's own "caller provides scratch" rule. The partial sums live in a 258 KB area built into the library
+ * (held by every GPU that loads it, until exit). Limits: C <= 512 channels, otherwise an error is returned; all
+ * calls on a device share that area, so calls that overlap on the GPU race — keep them on one stream. The first
+ * call on each device also resolves the area's device address; make that call before any stream capture begins.
+ * Allocates nothing (no cudaMalloc / cudaFree, no allocating library call). */
+int b200ddp_channel_sum_static(const float* dy, float* out, int Nb, int C, int HW, int device, void* stream);
+
 /* ---- C6: activations / pooling / dropout ------------------------------------------------------------ */
 /* Replace nn.ReLU + nn.MaxPool2d(3,2) (alexnet.py:23-24,26-27,33-34), nn.ReLU (:29,:31) and
  * nn.Dropout (:38,:41). NCHW fp32. idx: one byte per output, window slot 0..8, 255 = ReLU closed. */

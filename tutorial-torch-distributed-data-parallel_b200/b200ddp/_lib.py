@@ -65,6 +65,7 @@ _PROTOS = {
     "b200ddp_conv2d_weight_prep": (c_int, [_P, _P, c_int, c_int, c_int, c_int, c_longlong, c_int, c_int, _P]),
     "b200ddp_channel_sum_scratch_bytes": (c_longlong, [c_int, c_int]),
     "b200ddp_channel_sum": (c_int, [_P, _P, c_int, c_int, c_int, _P, c_longlong, c_int, _P]),
+    "b200ddp_channel_sum_static": (c_int, [_P, _P, c_int, c_int, c_int, c_int, _P]),
     "b200ddp_relu_maxpool_fwd": (c_int, [_P, _P, _P, c_int, c_int, c_int, c_int, c_int, c_int, _P]),
     "b200ddp_relu_maxpool_bwd": (c_int, [_P, _P, _P, c_int, c_int, c_int, c_int, c_int, _P]),
     "b200ddp_relu_fwd": (c_int, [_P, c_longlong, c_int, _P]),

@@ -31,6 +31,8 @@
 #include "tc.cuh"
 #include "../../include/b200ddp.h"
 
+#include <mutex>
+
 namespace b200 {
 
 namespace {
@@ -754,3 +756,69 @@ int b200ddp_channel_sum(const float* dy, float* out, int Nb, int C, int HW, void
 }
 
 }  // extern "C"
+
+namespace b200 {
+
+// ---------------------------------------------------------------------------------------------------------------
+// Channel sum for callers that have no device memory to lend as scratch.
+//
+// b200ddp_channel_sum() needs a caller-provided scratch buffer (per-CTA partial sums + one ticket per channel).
+// Some callers cannot produce one: code that runs where every byte of GPU memory already belongs to someone
+// else's pool and no allocator is reachable (a plugin called from inside another framework's step), or code on a
+// path where cudaMalloc is off limits because it synchronises the whole device and can fail under a memory cap.
+// For them the same kernel runs on a fixed scratch area that lives inside this library's device image.
+//
+// Cost and limits, so nobody is surprised:
+//   * the area is kStaticScratchBytes (258 KB) and every GPU that loads libb200ddp.so keeps it until the process
+//     exits, whether or not this entry point is ever called;
+//   * it fits at most kStaticMaxChannels (512) channels; larger C is refused with an error, not truncated;
+//   * all calls on a device share the one area and it keeps whatever the previous call left there. Each call
+//     re-zeroes the tickets it is about to use, but two calls that are in flight on the GPU at the same time
+//     (different streams, or different host threads feeding different streams) would trample each other's
+//     partial sums: issue them on one stream, or order them yourself;
+//   * the first call on a device looks the area's device address up (cudaGetSymbolAddress — the array name
+//     itself is only a host-side handle, not something a kernel may dereference) and remembers it. That lookup
+//     is a set-up step: make the first call on each device before you start capturing any stream.
+// ---------------------------------------------------------------------------------------------------------------
+namespace {
+constexpr int kStaticMaxChannels = 512;
+constexpr int kStaticMaxSplits = 64;                                   // cs_splits() never exceeds this
+constexpr long long kStaticTicketBytes = (long long)kStaticMaxChannels * 4;
+constexpr long long kStaticScratchBytes = kStaticTicketBytes + (long long)kStaticMaxChannels * kStaticMaxSplits * 8;
+constexpr int kStaticMaxDevices = 64;
+
+static __device__ __align__(256) unsigned char g_channel_sum_scratch[kStaticScratchBytes];
+
+std::mutex g_static_mu;
+void* g_static_base[kStaticMaxDevices] = {nullptr};    // per device: device address of g_channel_sum_scratch
+}  // namespace
+
+}  // namespace b200
+
+extern "C" int b200ddp_channel_sum_static(const float* dy, float* out, int Nb, int C, int HW, int device, void* stream) {
+  using namespace b200;
+  B200_CHECK_ARG(dy && out && Nb > 0 && C > 0 && HW > 0, "channel_sum_static: bad argument");
+  B200_CHECK_ARG(C <= kStaticMaxChannels,
+                 "channel_sum_static: C = %d channels do not fit the built-in scratch area (at most %d); "
+                 "use b200ddp_channel_sum with your own scratch buffer", C, kStaticMaxChannels);
+  B200_CHECK_ARG(device >= 0 && device < kStaticMaxDevices, "channel_sum_static: device ordinal %d out of range", device);
+  B200_DEVICE(device);                                   // `device` is current from here on
+  void* base = nullptr;
+  {
+    std::lock_guard<std::mutex> lk(g_static_mu);
+    if (!g_static_base[device]) {                        // first call on this device: one-time address lookup
+      void* ptr = nullptr;
+      B200_CUDA(cudaGetSymbolAddress(&ptr, g_channel_sum_scratch));
+      g_static_base[device] = ptr;
+    }
+    base = g_static_base[device];
+  }
+  const int S = cs_splits(Nb, C);                        // <= kStaticMaxSplits
+  unsigned int* tickets = reinterpret_cast<unsigned int*>(base);
+  double* partials = reinterpret_cast<double*>(reinterpret_cast<char*>(base) + kStaticTicketBytes);
+  // the area still holds the previous call's state: the tickets of the channels used now must start at zero
+  B200_CUDA(cudaMemsetAsync(tickets, 0, (size_t)C * sizeof(unsigned int), as_stream(stream)));
+  channel_sum_kernel<<<dim3(S, C), kCsThreads, 0, as_stream(stream)>>>(dy, Nb, C, HW, partials, tickets, out);
+  B200_LAUNCH_OK();
+  return 0;
+}
