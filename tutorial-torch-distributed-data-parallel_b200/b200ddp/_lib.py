@@ -162,3 +162,59 @@ def workspace(device, nbytes: int, tag: str = "ws", zero: bool = False):
                                                                                         device=device)
         _WORKSPACES[key] = buf
     return buf
+
+
+# ---- optional per-entry-point timing (used by bench.py for the roofline of the dominant kernel) ----------------
+_TIMING = None   # list of (entry point, int args, start event, end event) while enabled
+
+
+class _TimedLib:
+    """Proxy around the ctypes library: records a CUDA event before and after every kernel-launching entry point,
+    on the stream the call is issued on. Only bench.py turns it on; the events cost ~2 us of host time per call."""
+
+    _SKIP = ("_bytes", "last_error", "version", "launch_count", "device_info", "plan_buckets", "nccl_", "comm_create",
+             "comm_destroy", "comm_rank", "comm_unique_id")
+
+    def __init__(self, lib):
+        object.__setattr__(self, "_lib", lib)
+
+    def __getattr__(self, name):
+        fn = getattr(self._lib, name)
+        if _TIMING is None or any(t in name for t in self._SKIP):
+            return fn
+
+        def timed(*args):
+            # plain integer arguments (sizes, flags) identify the call; pointers / stream handles are > 2^40
+            ints = tuple(a for a in args if isinstance(a, int) and not isinstance(a, bool) and 0 <= a < (1 << 40))
+            e0 = torch.cuda.Event(enable_timing=True)
+            e1 = torch.cuda.Event(enable_timing=True)
+            e0.record()
+            rc = fn(*args)
+            e1.record()
+            _TIMING.append((name, ints, e0, e1))
+            return rc
+        return timed
+
+
+_PROXY = None
+
+
+def enable_timing() -> None:
+    """Start recording per-call CUDA events (calls made through _lib.load() after this point)."""
+    global _TIMING, _PROXY, _LIB
+    lib = load()
+    _TIMING = []
+    if not isinstance(lib, _TimedLib):
+        _PROXY = _TimedLib(lib)
+        _LIB = _PROXY
+
+
+def disable_timing() -> dict:
+    """Stop recording; returns [(entry_point, int_args, ms), ...] in call order (synchronises the device)."""
+    global _TIMING, _LIB
+    torch.cuda.synchronize()
+    out = [(name, ints, a.elapsed_time(b)) for name, ints, a, b in (_TIMING or [])]
+    _TIMING = None
+    if isinstance(_LIB, _TimedLib):
+        _LIB = object.__getattribute__(_LIB, "_lib")
+    return out

@@ -201,22 +201,9 @@ conv_fwd_kernel(const __grid_constant__ CUtensorMap tmW, ConvFwdParams p) {
     // ---------------- MMA issuer ----------------
     const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | (1u << 15) /* A MN-major */ |
                            ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(CBM >> 4) << 24);
-    for (int kb = 0; kb < p.kblocks; ++kb) {
-      const int s = kb % stages;
-      const uint32_t ph = (uint32_t)(kb / stages) & 1u;
-      mbar_wait(&full_bar[s], ph);
-      tc_fence_after();
-      const uint32_t sa = smem_u32(smem + (size_t)s * STAGE_BYTES);
-      const uint32_t sb = sa + A_BYTES;
-#pragma unroll
-      for (int k = 0; k < CBK / CUK; ++k) {
-        const uint64_t adesc = make_smem_desc(sa + k * 1024u, 4096u, 512u, 1u);
-        const uint64_t bdesc = make_smem_desc(sb + k * (CUK * 4), 16u, 1024u, 2u);
-        umma_tf32(tmem_base, adesc, bdesc, idesc, (kb > 0 || k > 0) ? 1u : 0u);
-      }
-      umma_commit(&empty_bar[s]);
-    }
-    umma_commit(tmem_full_bar);
+    mma_issue_loop<CBK / CUK>(tmem_base, idesc, smem_u32(smem), STAGE_BYTES, A_BYTES, operand_mn_major(),
+                              operand_k_major(), smem_u32(&full_bar[0]), smem_u32(&empty_bar[0]),
+                              smem_u32(tmem_full_bar), stages, p.kblocks);
   }
   tc_fence_before();
   __syncthreads();
@@ -402,22 +389,9 @@ conv_wgrad_kernel(ConvWgradParams p) {
     }
   } else if (lane == 0) {
     const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(CBM >> 4) << 24);
-    for (int i = 0; i < nkb; ++i) {
-      const int s = i % stages;
-      const uint32_t ph = (uint32_t)(i / stages) & 1u;
-      mbar_wait(&full_bar[s], ph);
-      tc_fence_after();
-      const uint32_t sa = smem_u32(smem + (size_t)s * STAGE_BYTES);
-      const uint32_t sb = sa + A_BYTES;
-#pragma unroll
-      for (int k = 0; k < CBK / CUK; ++k) {
-        const uint64_t adesc = make_smem_desc(sa + k * (CUK * 4), 16u, 1024u, 2u);
-        const uint64_t bdesc = make_smem_desc(sb + k * (CUK * 4), 16u, 1024u, 2u);
-        umma_tf32(tmem_base, adesc, bdesc, idesc, (i > 0 || k > 0) ? 1u : 0u);
-      }
-      umma_commit(&empty_bar[s]);
-    }
-    umma_commit(tmem_full_bar);
+    mma_issue_loop<CBK / CUK>(tmem_base, idesc, smem_u32(smem), STAGE_BYTES, A_BYTES, operand_k_major(),
+                              operand_k_major(), smem_u32(&full_bar[0]), smem_u32(&empty_bar[0]),
+                              smem_u32(tmem_full_bar), stages, nkb);
   }
   tc_fence_before();
   __syncthreads();

@@ -115,26 +115,10 @@ tf32_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                            | (2u << 7) | (2u << 10)       // A, B format = TF32
                            | ((uint32_t)p.a_mn << 15) | ((uint32_t)p.b_mn << 16)
                            | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
-    const uint32_t a_lbo = p.a_mn ? 4096u : 16u, a_sbo = p.a_mn ? 512u : 1024u;
-    const uint32_t a_adv = p.a_mn ? 1024u : (uint32_t)(UMMA_K * 4), a_lt = p.a_mn ? 1u : 2u;
-    const uint32_t b_lbo = p.b_mn ? 4096u : 16u, b_sbo = p.b_mn ? 512u : 1024u;
-    const uint32_t b_adv = p.b_mn ? 1024u : (uint32_t)(UMMA_K * 4), b_lt = p.b_mn ? 1u : 2u;
-    for (int i = 0; i < nkb; ++i) {
-      const int s = i % stages;
-      const uint32_t ph = (uint32_t)(i / stages) & 1u;
-      mbar_wait(&full_bar[s], ph);
-      tc_fence_after();
-      const uint32_t sa = smem_u32(smem + (size_t)s * STAGE_BYTES);
-      const uint32_t sb = sa + A_BYTES;
-#pragma unroll
-      for (int k = 0; k < BK / UMMA_K; ++k) {
-        const uint64_t adesc = make_smem_desc(sa + k * a_adv, a_lbo, a_sbo, a_lt);
-        const uint64_t bdesc = make_smem_desc(sb + k * b_adv, b_lbo, b_sbo, b_lt);
-        umma_tf32(tmem_base, adesc, bdesc, idesc, (i > 0 || k > 0) ? 1u : 0u);
-      }
-      umma_commit(&empty_bar[s]);        // frees this smem stage when the MMAs above retire
-    }
-    umma_commit(tmem_full_bar);          // accumulator complete -> epilogue may read TMEM
+    mma_issue_loop<BK / UMMA_K>(tmem_base, idesc, smem_u32(smem), STAGE_BYTES, A_BYTES,
+                                p.a_mn ? operand_mn_major() : operand_k_major(),
+                                p.b_mn ? operand_mn_major() : operand_k_major(), smem_u32(&full_bar[0]),
+                                smem_u32(&empty_bar[0]), smem_u32(tmem_full_bar), stages, nkb);
   } else if (warp >= 2) {
     // ---------------- epilogue: TMEM -> registers -> global ----------------
     mbar_wait(tmem_full_bar, 0);

@@ -115,5 +115,93 @@ __device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
 // make generic-proxy shared-memory writes (st.shared) visible to the async proxy (tcgen05.mma operand reads)
 __device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
+// named barrier among `count` threads of the CTA (ids 1..15; id 0 is __syncthreads)
+__device__ __forceinline__ void named_bar_sync(uint32_t id, uint32_t count) {
+  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(count) : "memory");
+}
+
+// ---- the MMA issuer's main loop -------------------------------------------------------------------------------
+// One thread walks the smem ring: wait full[s] -> UMMAS x tcgen05.mma -> tcgen05.commit(empty[s]).
+// Everything this thread executes is one dependent chain, so its instruction count per k-block bounds the
+// tile rate (measured with clock64 on B200: ~85 cycles per MMA when each descriptor is rebuilt from the stage
+// index, plus two runtime integer divisions for stage/phase - more than the tensor core needs for the MMA
+// itself at N <= 192). Hence: descriptors are advanced by adding to their low word (the 14-bit start-address
+// field, units of 16 B; smem addresses are < 256 KB so the sum never carries into the LBO field), stage and
+// phase are counters, and barrier addresses are running 32-bit shared addresses.
+struct OperandDesc {
+  uint32_t lbo, sbo, layout_type, k_advance;   // bytes, bytes, desc layout type, bytes between consecutive UMMA k-steps
+};
+__device__ __forceinline__ constexpr OperandDesc operand_k_major() { return {16u, 1024u, 2u, 32u}; }
+__device__ __forceinline__ constexpr OperandDesc operand_mn_major() { return {4096u, 512u, 1u, 1024u}; }
+
+__device__ __forceinline__ void umma_tf32_lohi(uint32_t tmem_d, uint32_t a_lo, uint32_t a_hi, uint32_t b_lo, uint32_t b_hi,
+                                               uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t.reg .b64 da, db;\n\t"
+      "setp.ne.b32 p, %6, 0;\n\t"
+      "mov.b64 da, {%1, %2};\n\t"
+      "mov.b64 db, {%3, %4};\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], da, db, %5, p;\n\t}"
+      ::"r"(tmem_d), "r"(a_lo), "r"(a_hi), "r"(b_lo), "r"(b_hi), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void umma_commit_addr(uint32_t bar_saddr) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar_saddr) : "memory");
+}
+__device__ __forceinline__ void mbar_wait_addr(uint32_t addr, uint32_t parity) {
+  uint32_t done = 0, spins = 0;
+  unsigned long long t0 = 0;
+  while (true) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(done)
+        : "r"(addr), "r"(parity)
+        : "memory");
+    if (done) break;
+    if ((++spins & 0x3ffu) == 0) {
+      const unsigned long long now = global_timer_ns();
+      if (t0 == 0) t0 = now;
+      else if (now - t0 > kWaitLimitNs) {
+        printf("b200ddp: mbarrier wait timed out (block %d,%d,%d thread %d parity %u)\n", blockIdx.x, blockIdx.y,
+               blockIdx.z, threadIdx.x, parity);
+        __trap();
+      }
+    }
+  }
+}
+
+// UMMAS = MMAs per k-block (BK / 8 for tf32). Stage layout: [A tile | B tile], stage_bytes apart.
+template <int UMMAS>
+__device__ __forceinline__ void mma_issue_loop(uint32_t tmem_d, uint32_t idesc, uint32_t smem_saddr, uint32_t stage_bytes,
+                                               uint32_t a_bytes, OperandDesc a, OperandDesc b, uint32_t full_saddr,
+                                               uint32_t empty_saddr, uint32_t tmem_full_saddr, int stages, int nkb) {
+  const uint32_t a_lo0 = ((smem_saddr & 0x3FFFFu) >> 4) | ((a.lbo >> 4) << 16);
+  const uint32_t b_lo0 = (((smem_saddr + a_bytes) & 0x3FFFFu) >> 4) | ((b.lbo >> 4) << 16);
+  const uint32_t a_hi = (a.sbo >> 4) | (1u << 14) | (a.layout_type << 29);
+  const uint32_t b_hi = (b.sbo >> 4) | (1u << 14) | (b.layout_type << 29);
+  const uint32_t a_step = a.k_advance >> 4, b_step = b.k_advance >> 4, stage_step = stage_bytes >> 4;
+  uint32_t a_lo = a_lo0, b_lo = b_lo0, fb = full_saddr, eb = empty_saddr, ph = 0, acc = 0;
+  int s = 0;
+#pragma unroll 1
+  for (int i = 0; i < nkb; ++i) {
+    mbar_wait_addr(fb, ph);
+    tc_fence_after();
+#pragma unroll
+    for (int k = 0; k < UMMAS; ++k) {
+      umma_tf32_lohi(tmem_d, a_lo + k * a_step, a_hi, b_lo + k * b_step, b_hi, idesc, acc);
+      acc = 1u;
+    }
+    umma_commit_addr(eb);                 // frees this smem stage when the MMAs above retire
+    if (++s == stages) {
+      s = 0; ph ^= 1u; a_lo = a_lo0; b_lo = b_lo0; fb = full_saddr; eb = empty_saddr;
+    } else {
+      a_lo += stage_step; b_lo += stage_step; fb += 8u; eb += 8u;
+    }
+  }
+  umma_commit_addr(tmem_full_saddr);      // accumulator complete -> epilogue may read TMEM
+}
+
 }  // namespace tc
 }  // namespace b200
