@@ -54,6 +54,9 @@ def parse():
 
 # ---- clocks ---------------------------------------------------------------------------------------------------
 class ClockSampler:
+    """SM clock + throttle reasons sampled DURING the timed regions: NVML polled every 5 ms from a thread
+    (a 30-step region lasts ~0.1 s), nvidia-smi -lms 20 as the fallback when pynvml cannot open the device."""
+    REASONS = (("hw_slowdown", 0x8), ("hw_thermal_slowdown", 0x40), ("sw_thermal_slowdown", 0x20), ("sw_power_cap", 0x4))
     QUERY = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
              "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
              "clocks_event_reasons.sw_power_cap")
@@ -62,14 +65,54 @@ class ClockSampler:
         self.index = index
         self.proc = None
         self.lines = []
+        self.samples = []          # (sm_mhz, reasons_mask)
+        self.max_mhz = None
+        self.stop_flag = threading.Event()
+        self.thread = None
+        self.source = None
+
+    def _nvml_handle(self):
+        import pynvml
+        pynvml.nvmlInit()
+        try:
+            import torch
+            uuid = str(torch.cuda.get_device_properties(self.index).uuid)
+            if not uuid.startswith("GPU-"):
+                uuid = "GPU-" + uuid
+            return pynvml, pynvml.nvmlDeviceGetHandleByUUID(uuid.encode())
+        except Exception:
+            return pynvml, pynvml.nvmlDeviceGetHandleByIndex(self.index)
+
+    def _poll(self, pynvml, h) -> None:
+        while not self.stop_flag.is_set():
+            try:
+                mhz = pynvml.nvmlDeviceGetClockInfo(h, pynvml.NVML_CLOCK_SM)
+                try:
+                    mask = pynvml.nvmlDeviceGetCurrentClocksEventReasons(h)
+                except Exception:
+                    mask = pynvml.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+                self.samples.append((float(mhz), int(mask)))
+            except Exception:
+                pass
+            time.sleep(0.005)
 
     def start(self) -> None:
         try:
+            pynvml, h = self._nvml_handle()
+            self.max_mhz = float(pynvml.nvmlDeviceGetMaxClockInfo(h, pynvml.NVML_CLOCK_SM))
+            self.thread = threading.Thread(target=self._poll, args=(pynvml, h), daemon=True)
+            self.thread.start()
+            self.source = "nvml 5 ms"
+            return
+        except Exception:
+            self.thread = None
+        try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.QUERY}",
-                                          "--format=csv,noheader,nounits", "-lms", "100"], stdout=subprocess.PIPE,
+                                          "--format=csv,noheader,nounits", "-lms", "20"], stdout=subprocess.PIPE,
                                          stderr=subprocess.DEVNULL, text=True)
             self.thread = threading.Thread(target=self._read, daemon=True)
             self.thread.start()
+            self.source = "nvidia-smi -lms 20"
         except Exception:
             self.proc = None
 
@@ -78,29 +121,43 @@ class ClockSampler:
             self.lines.append(line.strip())
 
     def stop(self) -> dict:
-        if self.proc is None:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        self.proc.terminate()
-        try:
-            self.proc.wait(timeout=2)
-        except Exception:
-            self.proc.kill()
+        if self.proc is None and not self.samples and self.source is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["clock sampling unavailable"]}
         sm, mx, reasons = [], [], set()
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for ln in self.lines:
-            f = [c.strip() for c in ln.split(",")]
-            if len(f) < 7:
-                continue
+        if self.proc is None:
+            self.stop_flag.set()
+            self.thread.join(timeout=1)
+            for mhz, mask in self.samples:
+                sm.append(mhz)
+                mx.append(self.max_mhz)
+                for n, bit in self.REASONS:
+                    if mask & bit:
+                        reasons.add(n)
+        else:
+            self.proc.terminate()
             try:
-                sm.append(float(f[0]))
-                mx.append(float(f[1]))
-            except ValueError:
-                continue
-            for n, v in zip(names, f[3:7]):
-                if v.lower().startswith("active"):
-                    reasons.add(n)
-        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": sorted(reasons), "samples": len(sm)}
+                self.proc.wait(timeout=2)
+            except Exception:
+                self.proc.kill()
+            names = [n for n, _ in self.REASONS]
+            order = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+            for ln in self.lines:
+                f = [c.strip() for c in ln.split(",")]
+                if len(f) < 7:
+                    continue
+                try:
+                    sm.append(float(f[0]))
+                    mx.append(float(f[1]))
+                except ValueError:
+                    continue
+                for n, v in zip(order, f[3:7]):
+                    if v.lower().startswith("active") and n in names:
+                        reasons.add(n)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no clock samples"], "source": self.source}
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2], "sm_min_mhz": sm[0], "sm_max_mhz": max(mx), "samples": len(sm),
+                "reasons": sorted(reasons), "source": self.source}
 
 
 # ---- reference arm ----------------------------------------------------------------------------------------------
@@ -203,6 +260,16 @@ def summarize_kernels(calls, steps: int):
     return out
 
 
+def ncu_traffic(label: str):
+    """DRAM bytes per launch of this kernel from the committed `ncu --set full` capture (profiles/ncu_traffic.json),
+    or None when that capture does not hold the kernel."""
+    try:
+        table = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
+        return table[label]["dram_bytes_per_launch"]
+    except Exception:
+        return None
+
+
 def roofline_of_dominant(kernels, hbm_peak, tf32_peak, peak_src, step_ms):
     """Roofline object for the entry point with the largest share of the step (measured with CUDA events)."""
     if not kernels:
@@ -212,11 +279,12 @@ def roofline_of_dominant(kernels, hbm_peak, tf32_peak, peak_src, step_ms):
     tensor_bound = ai > tf32_peak * 1e3 / hbm_peak        # arithmetic intensity above the machine balance point
     if tensor_bound and k["TFLOPs"]:
         return {"kernel": k["kernel"], "bound": "tensor", "achieved": k["TFLOPs"], "peak": tf32_peak, "unit": "TFLOP/s",
-                "frac": k["TFLOPs"] / tf32_peak, "traffic": None, "algorithmic_flops_per_launch": k["alg_flops_per_call"],
+                "frac": k["TFLOPs"] / tf32_peak, "traffic": ncu_traffic(k["kernel"]),
+                "algorithmic_bytes_per_launch": k["alg_bytes_per_call"], "algorithmic_flops_per_launch": k["alg_flops_per_call"],
                 "avg_launch_ms": k["ms_per_call"], "share_of_step": k["ms_per_step"] / step_ms,
                 "peak_source": "dense TF32 = bf16_tflops_sustained / 2 (MEASURED_PEAKS.json); operands are TF32"}
     return {"kernel": k["kernel"], "bound": "hbm", "achieved": k["GBps"], "peak": hbm_peak, "unit": "GB/s",
-            "frac": (k["GBps"] or 0.0) / hbm_peak, "traffic": None, "algorithmic_bytes_per_launch": k["alg_bytes_per_call"],
+            "frac": (k["GBps"] or 0.0) / hbm_peak, "traffic": ncu_traffic(k["kernel"]), "algorithmic_bytes_per_launch": k["alg_bytes_per_call"],
             "avg_launch_ms": k["ms_per_call"], "share_of_step": k["ms_per_step"] / step_ms, "peak_source": peak_src}
 
 
@@ -296,7 +364,7 @@ def run_b200(args) -> None:
     clocks = ClockSampler(local)
     if rank == 0:
         clocks.start()
-        time.sleep(0.15)
+        time.sleep(0.02)
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     adam_ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
     launches0 = _lib.launch_count()
@@ -319,7 +387,6 @@ def run_b200(args) -> None:
     ms = ev0.elapsed_time(ev1)
     final_loss = float(loss)
     adam_ms = [a.elapsed_time(b) for a, b in adam_ev]
-    clock_info = clocks.stop() if rank == 0 else None
     t = torch.tensor([ms], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -380,6 +447,7 @@ def run_b200(args) -> None:
     d2h = 4
 
     # ---- per-kernel CUDA-event timing of the same step (device-resident inputs), for the roofline of the dominant kernel ----
+    clock_info = clocks.stop() if rank == 0 else None      # covers both timed regions (resident and end to end)
     _lib.enable_timing()
     n_prof = min(args.steps, 10)
     for k in range(n_prof):
@@ -416,7 +484,7 @@ def run_b200(args) -> None:
             "roofline": roof,
             "roofline_adam": {"kernel": "adam_flat_kernel (O1: single-pass Adam over the flat arenas)", "bound": "hbm",
                               "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,
-                              "traffic": None, "algorithmic_bytes_per_launch": adam_bytes,
+                              "traffic": ncu_traffic(f"adam_step_flat n={n_arena}"), "algorithmic_bytes_per_launch": adam_bytes,
                               "avg_launch_ms": adam_t * 1e3, "peak_source": peak_src,
                               "share_of_step": adam_t * 1e3 / (ms_max / args.steps)},
             "kernels": kernels[:12],
