@@ -19,6 +19,8 @@ SOURCES = ["abi.cu", "adam.cu", "reduce.cu", "comm.cu", "plan.cu", "linear.cu", 
 
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
               "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr", "-Xptxas", "-v"]
+# developer builds only, e.g. B200DDP_NVCC_DEFINES=-DB200_CONV_TRACE (clock64 trace of one conv CTA, scripts/conv_trace.py)
+NVCC_FLAGS += [f for f in os.environ.get("B200DDP_NVCC_DEFINES", "").split() if f.startswith("-D")]
 
 
 def _nccl_include() -> str:

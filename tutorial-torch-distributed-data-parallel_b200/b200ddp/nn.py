@@ -146,8 +146,9 @@ _CONV_TABLES: dict = {}
 
 
 def _conv_tables(device, Cin: int, H: int, W: int, KH: int, KW: int):
-    """int32 device table of pairs indexed by k = (ci, kh, kw): {input offset, packed window position}.
-    Padded to a multiple of 128 pairs with an 'invalid' marker (host logic; built once per shape)."""
+    """int32 device table of pairs indexed by k = (ci, kh, kw): {input offset, window-position bits
+    1 << kh | 1 << (16 + kw)} (the kernels AND them with a per-pixel mask of in-image rows / columns).
+    Padded to a multiple of 128 pairs with {0, 1 << 31} = never valid (host logic; built once per shape)."""
     key = (str(device), Cin, H, W, KH, KW)
     t = _CONV_TABLES.get(key)
     if t is None:
@@ -157,9 +158,11 @@ def _conv_tables(device, Cin: int, H: int, W: int, KH: int, KW: int):
         ci, rem = k // (KH * KW), k % (KH * KW)
         kh, kw = rem // KW, rem % KW
         koff = (ci * H * W + kh * W + kw).to(torch.int32)
-        kpos = (kh | (kw << 16)).to(torch.int32)
+        if KH > 15 or KW > 15:
+            raise ValueError("b200ddp Conv2d (table path): kernel sizes above 15 are not supported")
+        kpos = ((1 << kh) | (1 << (16 + kw))).to(torch.int32)
         koff[K:] = 0
-        kpos[K:] = 0x7FFF7FFF
+        kpos[K:] = -(1 << 31)
         t = torch.stack([koff, kpos], dim=1).contiguous().to(device)
         _CONV_TABLES[key] = t
     return t

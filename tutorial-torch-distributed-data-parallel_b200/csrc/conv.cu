@@ -57,6 +57,33 @@ __device__ __forceinline__ void sts_f32(uint32_t addr, float v) {
   asm volatile("st.shared.f32 [%0], %1;" ::"r"(addr), "f"(v) : "memory");
 }
 
+// 32 loads base + r*stride (r < nvalid, zeros beyond). PLANE > 0: the stride is PLANE*4 bytes and becomes the
+// instruction's immediate offset; otherwise a 64-bit pointer walks by `stride4` (2 integer instructions per load).
+template <int PLANE>
+__device__ __forceinline__ void load_strided(const char* base, uint32_t stride4, int nvalid, float (&v)[32]) {
+  if (PLANE > 0) {
+    const float* q = reinterpret_cast<const float*>(base);
+    if (nvalid >= 32) {
+#pragma unroll
+      for (int r = 0; r < 32; ++r) v[r] = __ldg(q + r * PLANE);
+    } else {
+#pragma unroll
+      for (int r = 0; r < 32; ++r) {
+        v[r] = 0.f;
+        if (r < nvalid) v[r] = __ldg(q + r * PLANE);
+      }
+    }
+  } else {
+    const char* q = base;
+#pragma unroll
+    for (int r = 0; r < 32; ++r) {
+      v[r] = 0.f;
+      if (r < nvalid) v[r] = __ldg(reinterpret_cast<const float*>(q));
+      q += stride4;
+    }
+  }
+}
+
 template <int BN>
 constexpr uint32_t tmem_cols() { return BN <= 32 ? 32 : BN <= 64 ? 64 : BN <= 128 ? 128 : 256; }
 
@@ -64,14 +91,19 @@ struct ConvFwdParams {
   const float* x;
   float* y;
   const float* bias;
-  const int2* tab;     // k_order 0: [kblocks*32] {ci*H*W + kh*W + kw, kh | kw << 16 (0x7fff7fff beyond K)}
-  int Nb, Cin, H, W, Cout, OH, OW, KW, stride, pad;
+  const int2* tab;     // k_order 0: [kblocks*32] {ci*H*W + kh*W + kw, 1 << kh | 1 << (16 + kw)}; {0, 1 << 31} beyond K
+  int Nb, Cin, H, W, Cout, OH, OW, KH, KW, stride, pad;
   int kblocks, M, OHW, relu, stages;
+  long long* trace;    // B200_CONV_TRACE builds only: [kblocks][8] clock64 stamps of CTA (0,0); null otherwise
 };
 
-template <int BN, bool CI>
+// PL: -1 = table path (k_order 0); 0 = channel-inner path with a runtime channel stride; > 0 = channel-inner path
+// with the plane size H*W known at compile time (the toy model's 27x27 and 13x13 planes), so that the 32 loads
+// of a k-block are `LDG [base + immediate]` with no address arithmetic at all.
+template <int BN, int PL>
 __global__ void __launch_bounds__(kConvThreads, 1)
 conv_fwd_kernel(const __grid_constant__ CUtensorMap tmW, ConvFwdParams p) {
+  constexpr bool CI = PL >= 0;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   constexpr uint32_t A_BYTES = CBM * CBK * 4;
@@ -111,7 +143,8 @@ conv_fwd_kernel(const __grid_constant__ CUtensorMap tmW, ConvFwdParams p) {
     const int oh = pix / p.OW, ow = pix - oh * p.OW;
     const int ih0 = oh * p.stride - p.pad, iw0 = ow * p.stride - p.pad;
     const long long hw = (long long)p.H * p.W;
-    const float* xb = p.x + ((long long)n_img * p.Cin * hw + (long long)ih0 * p.W + iw0);
+    const uint32_t hw4 = (uint32_t)hw * 4u;                 // byte stride between channels
+    const char* xb = reinterpret_cast<const char*>(p.x + ((long long)n_img * p.Cin * hw + (long long)ih0 * p.W + iw0));
     // MN-major SWIZZLE_128B_BASE32B: k-row r at r*128 B, 32-byte chunk c stored at chunk c ^ (r & 3);
     // the 32-pixel atom `gwarp` starts at gwarp*4096 B.
     const uint32_t chunk = (uint32_t)lane >> 3;
@@ -119,48 +152,83 @@ conv_fwd_kernel(const __grid_constant__ CUtensorMap tmW, ConvFwdParams p) {
     uint32_t s_chunk[4];
 #pragma unroll
     for (int c = 0; c < 4; ++c) s_chunk[c] = s_thread + ((chunk ^ (uint32_t)c) << 5);
+    // The producer loops are bound by instruction issue (ncu: 13 instructions per gathered element before this
+    // was restructured), so everything that can be hoisted is: the reduction cursor (kh, kw, channel block) and the
+    // smem ring cursor (stage, phase) advance by additions, the per-element address is one IMAD.WIDE
+    // (base + r * channel stride), and in the table path the bounds test is one AND + compare against a per-thread
+    // mask of valid window rows / columns.
     const int cb = CI ? (p.Cin >> 5) : 1;      // channel blocks per (kh, kw)
+    int cur_cblk = 0, cur_kh = 0, cur_kw = 0;  // CI: position of this group's next k-block to LOAD
+    if (CI) {
+      const int khkw = group / cb;
+      cur_cblk = group - khkw * cb;
+      cur_kh = khkw / p.KW;
+      cur_kw = khkw - cur_kh * p.KW;
+    }
+    uint32_t win_mask = 0;                     // table path: bit kh = window row inside the image, bit 16+kw = column
+    if (!CI && valid_m) {
+      auto span = [](int i0, int n, int limit) -> uint32_t {
+        const int lo = i0 < 0 ? -i0 : 0;
+        int hi = limit - i0;
+        hi = hi > n ? n : hi;
+        return hi > lo ? (((1u << hi) - 1u) & ~((1u << lo) - 1u)) : 0u;
+      };
+      win_mask = span(ih0, p.KH, p.H) | (span(iw0, p.KW, p.W) << 16);
+    }
     // Software pipeline in registers: the 32 loads of this group's NEXT k-block are issued before the current
-    // one is stored, and before its smem slot is even free — loads never wait for the MMA, stores never wait
+    // one is stored, and before its smem slot is even free - loads never wait for the MMA, stores never wait
     // for DRAM/L2 (the data arrived while the previous block was being stored).
+#ifdef B200_CONV_TRACE
+    const bool tr = p.trace && blockIdx.x == 0 && blockIdx.y == 0 && gtid == 0;
+#define B200_TRACE(kb, slot) if (tr) p.trace[(kb) * 8 + (slot)] = clock64()
+#else
+#define B200_TRACE(kb, slot)
+#endif
     auto issue = [&](int kb, float (&v)[CBK]) {
+      B200_TRACE(kb, 0);
       if (CI) {
-        const int khkw = kb / cb, ci0 = (kb - khkw * cb) << 5;
-        const int kh = khkw / p.KW, kw = khkw - kh * p.KW;
-        const bool ok = valid_m && (unsigned)(ih0 + kh) < (unsigned)p.H && (unsigned)(iw0 + kw) < (unsigned)p.W;
-        const float* q = xb + ((long long)ci0 * hw + kh * p.W + kw);
-#pragma unroll
-        for (int r = 0; r < CBK; ++r) {       // constant stride H*W between channels
-          v[r] = 0.f;
-          if (ok) v[r] = __ldg(q);
-          q += hw;
+        const bool ok = valid_m && (unsigned)(ih0 + cur_kh) < (unsigned)p.H && (unsigned)(iw0 + cur_kw) < (unsigned)p.W;
+        const char* q = xb + (((long long)(cur_cblk << 5) * hw + cur_kh * p.W + cur_kw) << 2);
+        load_strided<PL>(q, hw4, ok ? CBK : 0, v);     // constant stride H*W between channels
+        cur_cblk += kGroups;
+        while (cur_cblk >= cb) {
+          cur_cblk -= cb;
+          if (++cur_kw == p.KW) { cur_kw = 0; ++cur_kh; }
         }
       } else {
         const int2* tab = p.tab + kb * CBK;
 #pragma unroll
         for (int r = 0; r < CBK; ++r) {
           const int2 t = __ldg(tab + r);      // uniform address: one broadcast transaction per warp
-          const int ih = ih0 + (t.y & 0xffff), iw = iw0 + (t.y >> 16);
-          const bool ok = valid_m && (unsigned)ih < (unsigned)p.H && (unsigned)iw < (unsigned)p.W;
           v[r] = 0.f;
-          if (ok) v[r] = __ldg(xb + t.x);
+          if ((win_mask & (uint32_t)t.y) == (uint32_t)t.y)
+            v[r] = __ldg(reinterpret_cast<const float*>(xb + ((unsigned long long)(uint32_t)t.x << 2)));
         }
       }
     };
+    int c_stage = group;                       // ring cursor of this group's next k-block to STORE (stages >= kGroups)
+    uint32_t c_phase = 0;
     auto commit = [&](int kb, const float (&v)[CBK]) {
-      const int s = kb % stages;
-      const uint32_t ph = (uint32_t)(kb / stages) & 1u;
-      mbar_wait(&empty_bar[s], ph ^ 1u);
-      uint8_t* sa = smem + (size_t)s * STAGE_BYTES;
+      B200_TRACE(kb, 6);
+      mbar_wait(&empty_bar[c_stage], c_phase ^ 1u);
+      B200_TRACE(kb, 1);
+      uint8_t* sa = smem + (size_t)c_stage * STAGE_BYTES;
       if (gtid == 0) {
-        mbar_expect_tx(&full_bar[s], B_BYTES);
-        tma_load_2d(sa + A_BYTES, &tmW, &full_bar[s], kb * CBK, n0);       // box {32 k, BN co}
+        mbar_expect_tx(&full_bar[c_stage], B_BYTES);
+        tma_load_2d(sa + A_BYTES, &tmW, &full_bar[c_stage], kb * CBK, n0);       // box {32 k, BN co}
       }
       const uint32_t sdst = smem_u32(sa);
+      uint32_t sd[4];
 #pragma unroll
-      for (int r = 0; r < CBK; ++r) sts_f32(sdst + s_chunk[r & 3] + (uint32_t)r * 128u, round_tf32(v[r]));
+      for (int c = 0; c < 4; ++c) sd[c] = sdst + s_chunk[c];
+#pragma unroll
+      for (int r = 0; r < CBK; ++r) sts_f32(sd[r & 3] + (uint32_t)r * 128u, round_tf32(v[r]));
+      B200_TRACE(kb, 7);
       fence_proxy_async_smem();
-      mbar_arrive(&full_bar[s]);
+      mbar_arrive(&full_bar[c_stage]);
+      B200_TRACE(kb, 2);
+      c_stage += kGroups;
+      if (c_stage >= stages) { c_stage -= stages; c_phase ^= 1u; }
     };
     {
       float va[CBK], vb[CBK];
@@ -197,13 +265,14 @@ conv_fwd_kernel(const __grid_constant__ CUtensorMap tmW, ConvFwdParams p) {
         }
       }
     }
-  } else if (lane == 0) {
+  } else {
     // ---------------- MMA issuer ----------------
     const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | (1u << 15) /* A MN-major */ |
                            ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(CBM >> 4) << 24);
     mma_issue_loop<CBK / CUK>(tmem_base, idesc, smem_u32(smem), STAGE_BYTES, A_BYTES, operand_mn_major(),
                               operand_k_major(), smem_u32(&full_bar[0]), smem_u32(&empty_bar[0]),
-                              smem_u32(tmem_full_bar), stages, p.kblocks);
+                              smem_u32(tmem_full_bar), stages, p.kblocks,
+                              (blockIdx.x == 0 && blockIdx.y == 0) ? p.trace : nullptr);
   }
   tc_fence_before();
   __syncthreads();
@@ -215,14 +284,15 @@ struct ConvWgradParams {
   const float* dy;
   float* out;          // gradient matrix [Cout][K] in GEMM k order (splits == 1, k_order 0) or partials [z][Cout][K]
   float* dw_direct;    // k_order 1 and splits == 1: dW in torch order, written with the permuted index
-  const int2* tab;     // k_order 0: [m_tiles*128] {input offset, kh | kw << 16}
+  const int2* tab;     // k_order 0: [m_tiles*128] {input offset, 1 << kh | 1 << (16 + kw)}; {0, 1 << 31} beyond K
   int Nb, Cin, H, W, Cout, OH, OW, KH, KW, stride, pad;
   int K, M, OHW, kblocks_total, kblocks_per_split, splits, stages;
 };
 
-template <int BN, bool CI>
+template <int BN, int PL>       // PL as in conv_fwd_kernel; PL > 0 additionally means OH*OW == H*W == PL
 __global__ void __launch_bounds__(kWgThreads, 1)
 conv_wgrad_kernel(ConvWgradParams p) {
+  constexpr bool CI = PL >= 0;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   constexpr uint32_t A_BYTES = CBM * CBK * 4;
@@ -263,6 +333,8 @@ conv_wgrad_kernel(ConvWgradParams p) {
     const int group = warp >> 2, gwarp = warp & 3;
     constexpr int B_ROWS = BN / 4;
     const long long hw = (long long)p.H * p.W;
+    const uint32_t hw4 = (uint32_t)hw * 4u, ohw4 = (uint32_t)p.OHW * 4u;      // byte strides between channels
+    const float inv_ohw = 1.0f / (float)p.OHW, inv_ow = 1.0f / (float)p.OW;
     // K-major SWIZZLE_128B: row i at i*128 B, 16-byte chunk c stored at chunk c ^ (i & 7)
     const uint32_t c16 = (uint32_t)lane >> 2, e16 = ((uint32_t)lane & 3u) * 4u;
     uint32_t s_chunk[8];
@@ -274,79 +346,94 @@ conv_wgrad_kernel(ConvWgradParams p) {
     const int khkw_w = CI ? (rows_valid ? k0 / p.Cin : 0) : 0;
     const int ci0_w = CI ? (rows_valid ? k0 - khkw_w * p.Cin : 0) : 0;
     const int kh_w = khkw_w / p.KW, kw_w = khkw_w - kh_w * p.KW;
+    const long long a_off = CI ? (((long long)ci0_w * hw + kh_w * p.W + kw_w) << 2) : 0;   // bytes, constant per warp
     // Work of one k-block for a thread = batches of <= 32 loads: [A rows] [B rows 0..31] [B rows 32..].
     // Software pipeline in registers: the loads of the NEXT batch are issued before the current batch is stored
     // (and before the current k-block's smem slot is known to be free), so a batch of loads is always in flight.
+    // Instruction economy as in the forward kernel: cursors advance by additions, pixel -> (image, row, column)
+    // uses float reciprocals (exact: pixel index < 2^23, quotient error << 1/(2*OHW)), one IMAD.WIDE per address.
     constexpr int NB = 1 + (B_ROWS + 31) / 32;
     int li = group, lt = 0;            // load cursor: (k-block, batch)
-    int si = group, st_ = 0;           // store cursor
-    bool l_valid = false, l_okA = false;
-    const float* l_xq = p.x;
-    const float* l_dyb = p.dy;
+    int l_pxl = kb_begin * CBK + group * CBK + lane;   // pixel of this lane in k-block li
+    bool l_valid = false;
+    const char* l_dyb = reinterpret_cast<const char*>(p.dy);
     auto load = [&](float (&v)[32]) {
       if (lt == 0) {
-        const int pxl = (kb_begin + li) * CBK + lane;
-        l_valid = pxl < p.M;
-        const int pp = l_valid ? pxl : 0;
-        const int n_img = pp / p.OHW, pix = pp - n_img * p.OHW;
-        const int oh = pix / p.OW, ow = pix - oh * p.OW;
+        l_valid = l_pxl < p.M;
+        const int pp = l_valid ? l_pxl : 0;
+        int n_img = (int)(((float)pp + 0.5f) * inv_ohw), pix = pp - n_img * p.OHW;
+        if (pix < 0) { --n_img; pix += p.OHW; } else if (pix >= p.OHW) { ++n_img; pix -= p.OHW; }   // never taken at these sizes
+        int oh = (int)(((float)pix + 0.5f) * inv_ow), ow = pix - oh * p.OW;
+        if (ow < 0) { --oh; ow += p.OW; } else if (ow >= p.OW) { ++oh; ow -= p.OW; }
         const int ih0 = oh * p.stride - p.pad, iw0 = ow * p.stride - p.pad;
-        const float* xb = p.x + ((long long)n_img * p.Cin * hw + (long long)ih0 * p.W + iw0);
-        l_dyb = p.dy + (long long)n_img * p.Cout * p.OHW + pix;
+        const char* xb = reinterpret_cast<const char*>(p.x + ((long long)n_img * p.Cin * hw + (long long)ih0 * p.W + iw0));
+        l_dyb = reinterpret_cast<const char*>(p.dy + ((long long)n_img * p.Cout * p.OHW + pix));
+        l_pxl += kWgGroups * CBK;
         if (CI) {
-          l_okA = l_valid && rows_valid && (unsigned)(ih0 + kh_w) < (unsigned)p.H && (unsigned)(iw0 + kw_w) < (unsigned)p.W;
-          const float* q = xb + ((long long)ci0_w * hw + kh_w * p.W + kw_w);
-#pragma unroll
-          for (int j = 0; j < 32; ++j) {
-            v[j] = 0.f;
-            if (l_okA) v[j] = __ldg(q);
-            q += hw;
-          }
+          const bool ok = l_valid && rows_valid && (unsigned)(ih0 + kh_w) < (unsigned)p.H && (unsigned)(iw0 + kw_w) < (unsigned)p.W;
+          const char* q = xb + a_off;
+          load_strided<PL>(q, hw4, ok ? 32 : 0, v);
         } else {
+          uint32_t win_mask = 0;
+          if (l_valid) {
+            auto span = [](int i0, int n, int limit) -> uint32_t {
+              const int lo = i0 < 0 ? -i0 : 0;
+              int hi = limit - i0;
+              hi = hi > n ? n : hi;
+              return hi > lo ? (((1u << hi) - 1u) & ~((1u << lo) - 1u)) : 0u;
+            };
+            win_mask = span(ih0, p.KH, p.H) | (span(iw0, p.KW, p.W) << 16);
+          }
 #pragma unroll
           for (int j = 0; j < 32; ++j) {
             const int2 t = s_tab[gwarp * 32 + j];
-            const int ih = ih0 + (t.y & 0xffff), iw = iw0 + (t.y >> 16);
-            const bool ok = l_valid && (unsigned)ih < (unsigned)p.H && (unsigned)iw < (unsigned)p.W;
             v[j] = 0.f;
-            if (ok) v[j] = __ldg(xb + t.x);
+            if ((win_mask & (uint32_t)t.y) == (uint32_t)t.y)
+              v[j] = __ldg(reinterpret_cast<const float*>(xb + ((unsigned long long)(uint32_t)t.x << 2)));
           }
         }
       } else {
         const int r0 = (lt - 1) * 32;
         const int co0 = n0 + gwarp * B_ROWS + r0;
-        const float* q = l_dyb + (long long)co0 * p.OHW;
-#pragma unroll
-        for (int j = 0; j < 32; ++j) {
-          v[j] = 0.f;
-          if (r0 + j < B_ROWS && l_valid && co0 + j < p.Cout) v[j] = __ldg(q);
-          q += p.OHW;
-        }
+        int nrows = B_ROWS - r0;                       // rows of this batch that exist in the tile and the tensor
+        if (nrows > p.Cout - co0) nrows = p.Cout - co0;
+        if (!l_valid) nrows = 0;
+        const char* q = l_dyb + (unsigned long long)ohw4 * (unsigned)co0;
+        load_strided<PL>(q, ohw4, nrows, v);
       }
       if (++lt == NB) { lt = 0; li += kWgGroups; }
     };
+    int si = group, st_ = 0;           // store cursor: (k-block, batch)
+    int c_stage = group;               // its ring slot and phase (stages >= kWgGroups)
+    uint32_t c_phase = 0;
     auto store = [&](const float (&v)[32]) {
-      const int s = si % stages;
-      const uint32_t sa = smem_u32(smem + (size_t)s * STAGE_BYTES);
+      const uint32_t sa = smem_u32(smem + (size_t)c_stage * STAGE_BYTES);
       if (st_ == 0) {
-        mbar_wait(&empty_bar[s], ((uint32_t)(si / stages) & 1u) ^ 1u);
+        mbar_wait(&empty_bar[c_stage], c_phase ^ 1u);
+        uint32_t sd[8];
+#pragma unroll
+        for (int c = 0; c < 8; ++c) sd[c] = sa + (uint32_t)(gwarp * 32) * 128u + s_chunk[c];
 #pragma unroll
         for (int j = 0; j < 32; ++j)      // (gwarp*32 + j) & 7 == j & 7
-          sts_f32(sa + (uint32_t)(gwarp * 32 + j) * 128u + s_chunk[j & 7], round_tf32(v[j]));
+          sts_f32(sd[j & 7] + (uint32_t)j * 128u, round_tf32(v[j]));
       } else {
         const int r0 = (st_ - 1) * 32;
-        const uint32_t sb = sa + A_BYTES;
+        const int nrows = B_ROWS - r0;
+        uint32_t sd[8];
 #pragma unroll
-        for (int j = 0; j < 32; ++j) {
-          const int row = gwarp * B_ROWS + r0 + j;      // B_ROWS and r0 are multiples of 8 -> row & 7 == j & 7
-          if (r0 + j < B_ROWS) sts_f32(sb + (uint32_t)row * 128u + s_chunk[j & 7], round_tf32(v[j]));
-        }
+        for (int c = 0; c < 8; ++c)       // B_ROWS and r0 are multiples of 8 -> row & 7 == j & 7
+          sd[c] = sa + A_BYTES + (uint32_t)(gwarp * B_ROWS + r0) * 128u + s_chunk[c];
+#pragma unroll
+        for (int j = 0; j < 32; ++j)
+          if (j < nrows) sts_f32(sd[j & 7] + (uint32_t)j * 128u, round_tf32(v[j]));
       }
       if (++st_ == NB) {
         fence_proxy_async_smem();
-        mbar_arrive(&full_bar[s]);
+        mbar_arrive(&full_bar[c_stage]);
         st_ = 0;
         si += kWgGroups;
+        c_stage += kWgGroups;
+        if (c_stage >= stages) { c_stage -= stages; c_phase ^= 1u; }
       }
     };
     {
@@ -387,7 +474,7 @@ conv_wgrad_kernel(ConvWgradParams p) {
         }
       }
     }
-  } else if (lane == 0) {
+  } else {
     const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(CBM >> 4) << 24);
     mma_issue_loop<CBK / CUK>(tmem_base, idesc, smem_u32(smem), STAGE_BYTES, A_BYTES, operand_k_major(),
                               operand_k_major(), smem_u32(&full_bar[0]), smem_u32(&empty_bar[0]),
@@ -493,13 +580,13 @@ inline int cs_splits(int Nb, int C) {
   return s < 1 ? 1 : s;
 }
 
-template <int BN, bool CI>
+template <int BN, int PL>
 int launch_fwd(const CUtensorMap& tmW, const ConvFwdParams& p, cudaStream_t stream) {
   const size_t stage_bytes = (size_t)(CBM + BN) * CBK * 4;
   const size_t smem = 1024 + (size_t)p.stages * stage_bytes + (2 * p.stages + 1) * 8 + 16;
   static bool attr_set = false;
   if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(conv_fwd_kernel<BN, CI>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    cudaError_t e = cudaFuncSetAttribute(conv_fwd_kernel<BN, PL>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
     if (e != cudaSuccess) {
       set_error("cudaFuncSetAttribute(conv_fwd_kernel<%d>) -> %s", BN, cudaGetErrorString(e));
       return kCudaErrBase + (int)e;
@@ -507,7 +594,7 @@ int launch_fwd(const CUtensorMap& tmW, const ConvFwdParams& p, cudaStream_t stre
     attr_set = true;
   }
   dim3 grid((p.M + CBM - 1) / CBM, (p.Cout + BN - 1) / BN, 1);
-  conv_fwd_kernel<BN, CI><<<grid, kConvThreads, smem, stream>>>(tmW, p);
+  conv_fwd_kernel<BN, PL><<<grid, kConvThreads, smem, stream>>>(tmW, p);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) {
     set_error("conv_fwd_kernel<%d> launch (grid %d,%d smem %zu) -> %s", BN, grid.x, grid.y, smem, cudaGetErrorString(e));
@@ -517,13 +604,13 @@ int launch_fwd(const CUtensorMap& tmW, const ConvFwdParams& p, cudaStream_t stre
   return 0;
 }
 
-template <int BN, bool CI>
+template <int BN, int PL>
 int launch_wgrad(const ConvWgradParams& p, cudaStream_t stream) {
   const size_t stage_bytes = (size_t)(CBM + BN) * CBK * 4;
   const size_t smem = 1024 + (size_t)p.stages * stage_bytes + (2 * p.stages + 1) * 8 + 32 + CBM * 8;
   static bool attr_set = false;
   if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(conv_wgrad_kernel<BN, CI>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    cudaError_t e = cudaFuncSetAttribute(conv_wgrad_kernel<BN, PL>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
     if (e != cudaSuccess) {
       set_error("cudaFuncSetAttribute(conv_wgrad_kernel<%d>) -> %s", BN, cudaGetErrorString(e));
       return kCudaErrBase + (int)e;
@@ -531,7 +618,7 @@ int launch_wgrad(const ConvWgradParams& p, cudaStream_t stream) {
     attr_set = true;
   }
   dim3 grid((p.K + CBM - 1) / CBM, (p.Cout + BN - 1) / BN, p.splits);
-  conv_wgrad_kernel<BN, CI><<<grid, kWgThreads, smem, stream>>>(p);
+  conv_wgrad_kernel<BN, PL><<<grid, kWgThreads, smem, stream>>>(p);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) {
     set_error("conv_wgrad_kernel<%d> launch (grid %d,%d,%d smem %zu) -> %s", BN, grid.x, grid.y, grid.z, smem,
@@ -579,6 +666,11 @@ inline WgradPlan plan_wgrad(int Nb, int Cin, int OH, int OW, int Cout, int KH, i
 
 using namespace b200;
 
+#ifdef B200_CONV_TRACE
+static long long* g_conv_trace = nullptr;
+extern "C" int b200ddp_debug_conv_trace(long long* dev_buf) { g_conv_trace = dev_buf; return 0; }
+#endif
+
 extern "C" {
 
 int b200ddp_conv2d_fwd(const float* x, const float* wmat, long long ldw, const float* bias, float* y, const int* ktab,
@@ -588,6 +680,7 @@ int b200ddp_conv2d_fwd(const float* x, const float* wmat, long long ldw, const f
   B200_CHECK_ARG(k_order == 0 || k_order == 1, "conv2d_fwd: k_order must be 0 (ci,kh,kw) or 1 (kh,kw,ci)");
   B200_CHECK_ARG(k_order == 1 || (ktab && ((uintptr_t)ktab & 7) == 0), "conv2d_fwd: k_order 0 needs an 8-byte aligned ktab");
   B200_CHECK_ARG(k_order == 0 || (Cin % 32) == 0, "conv2d_fwd: k_order 1 needs Cin %% 32 == 0 (Cin = %d)", Cin);
+  B200_CHECK_ARG(k_order == 1 || (KH <= 15 && KW <= 15), "conv2d_fwd: k_order 0 supports kernel sizes up to 15 (got %dx%d)", KH, KW);
   B200_CHECK_ARG(Nb > 0 && Cin > 0 && Cout > 0 && KH > 0 && KW > 0 && stride > 0 && pad >= 0, "conv2d_fwd: bad shape");
   B200_CHECK_ARG((ldw & 3) == 0 && ((uintptr_t)wmat & 15) == 0, "conv2d_fwd: weight rows must be 16-byte aligned (ldw %% 4 == 0)");
   const int OH = (H + 2 * pad - KH) / stride + 1, OW = (W + 2 * pad - KW) / stride + 1;
@@ -597,9 +690,13 @@ int b200ddp_conv2d_fwd(const float* x, const float* wmat, long long ldw, const f
   const int K = Cin * KH * KW;
   ConvFwdParams p;
   p.x = x; p.y = y; p.bias = bias; p.tab = reinterpret_cast<const int2*>(ktab);
-  p.Nb = Nb; p.Cin = Cin; p.H = H; p.W = W; p.Cout = Cout; p.OH = OH; p.OW = OW; p.KW = KW; p.stride = stride; p.pad = pad;
+  p.Nb = Nb; p.Cin = Cin; p.H = H; p.W = W; p.Cout = Cout; p.OH = OH; p.OW = OW; p.KH = KH; p.KW = KW; p.stride = stride; p.pad = pad;
   p.kblocks = (K + CBK - 1) / CBK;
   p.M = Nb * OH * OW; p.OHW = OH * OW; p.relu = relu;
+  p.trace = nullptr;
+#ifdef B200_CONV_TRACE
+  p.trace = g_conv_trace;
+#endif
   const int bn = pick_bn(Cout);
   const size_t stage_bytes = (size_t)(CBM + bn) * CBK * 4;
   int stages = (int)((200 * 1024) / stage_bytes);
@@ -611,20 +708,21 @@ int b200ddp_conv2d_fwd(const float* x, const float* wmat, long long ldw, const f
   int rc = tma_map_2d(&tmW, wmat, ldw, Cout, ldw, CBK, bn, 0);
   if (rc) return rc;
   cudaStream_t s = as_stream(stream);
+#define B200_FWD_BN(PLV)                                         \
+  switch (bn) {                                                  \
+    case 64: return launch_fwd<64, PLV>(tmW, p, s);              \
+    case 128: return launch_fwd<128, PLV>(tmW, p, s);            \
+    case 192: return launch_fwd<192, PLV>(tmW, p, s);            \
+    default: return launch_fwd<256, PLV>(tmW, p, s);             \
+  }
   if (k_order == 1) {
-    switch (bn) {
-      case 64: return launch_fwd<64, true>(tmW, p, s);
-      case 128: return launch_fwd<128, true>(tmW, p, s);
-      case 192: return launch_fwd<192, true>(tmW, p, s);
-      default: return launch_fwd<256, true>(tmW, p, s);
-    }
+    const int plane = H * W;
+    if (plane == 27 * 27) { B200_FWD_BN(27 * 27) }
+    if (plane == 13 * 13) { B200_FWD_BN(13 * 13) }
+    B200_FWD_BN(0)
   }
-  switch (bn) {
-    case 64: return launch_fwd<64, false>(tmW, p, s);
-    case 128: return launch_fwd<128, false>(tmW, p, s);
-    case 192: return launch_fwd<192, false>(tmW, p, s);
-    default: return launch_fwd<256, false>(tmW, p, s);
-  }
+  B200_FWD_BN(-1)
+#undef B200_FWD_BN
 }
 
 long long b200ddp_conv2d_wgrad_workspace_bytes(int Nb, int Cin, int H, int W, int Cout, int KH, int KW, int stride,
@@ -641,6 +739,7 @@ int b200ddp_conv2d_wgrad(const float* x, const float* dy, float* dw, const int* 
   B200_CHECK_ARG(k_order == 0 || k_order == 1, "conv2d_wgrad: k_order must be 0 or 1");
   B200_CHECK_ARG(k_order == 1 || (ktab && ((uintptr_t)ktab & 7) == 0), "conv2d_wgrad: k_order 0 needs an 8-byte aligned ktab");
   B200_CHECK_ARG(k_order == 0 || (Cin % 32) == 0, "conv2d_wgrad: k_order 1 needs Cin %% 32 == 0 (Cin = %d)", Cin);
+  B200_CHECK_ARG(k_order == 1 || (KH <= 15 && KW <= 15), "conv2d_wgrad: k_order 0 supports kernel sizes up to 15 (got %dx%d)", KH, KW);
   const int OH = (H + 2 * pad - KH) / stride + 1, OW = (W + 2 * pad - KW) / stride + 1;
   B200_CHECK_ARG(OH > 0 && OW > 0 && Nb > 0, "conv2d_wgrad: bad shape");
   B200_CHECK_ARG((long long)Nb * OH * OW < (1ll << 31) && (long long)Cin * H * W < (1ll << 31), "conv2d_wgrad: tensor too large");
@@ -664,21 +763,22 @@ int b200ddp_conv2d_wgrad(const float* x, const float* dy, float* dw, const int* 
   p.stages = stages;
   cudaStream_t s = as_stream(stream);
   int rc;
-  if (k_order == 1) {
-    switch (w.bn) {
-      case 64: rc = launch_wgrad<64, true>(p, s); break;
-      case 128: rc = launch_wgrad<128, true>(p, s); break;
-      case 192: rc = launch_wgrad<192, true>(p, s); break;
-      default: rc = launch_wgrad<256, true>(p, s); break;
-    }
-  } else {
-    switch (w.bn) {
-      case 64: rc = launch_wgrad<64, false>(p, s); break;
-      case 128: rc = launch_wgrad<128, false>(p, s); break;
-      case 192: rc = launch_wgrad<192, false>(p, s); break;
-      default: rc = launch_wgrad<256, false>(p, s); break;
-    }
+#define B200_WG_BN(PLV)                                          \
+  switch (w.bn) {                                                \
+    case 64: rc = launch_wgrad<64, PLV>(p, s); break;            \
+    case 128: rc = launch_wgrad<128, PLV>(p, s); break;          \
+    case 192: rc = launch_wgrad<192, PLV>(p, s); break;          \
+    default: rc = launch_wgrad<256, PLV>(p, s); break;           \
   }
+  if (k_order == 1) {
+    const int plane = (H * W == OH * OW) ? H * W : 0;            // the compile-time stride serves x and dy
+    if (plane == 27 * 27) { B200_WG_BN(27 * 27) }
+    else if (plane == 13 * 13) { B200_WG_BN(13 * 13) }
+    else { B200_WG_BN(0) }
+  } else {
+    B200_WG_BN(-1)
+  }
+#undef B200_WG_BN
   if (rc) return rc;
   if (w.splits > 1) {
     if (k_order == 1) {

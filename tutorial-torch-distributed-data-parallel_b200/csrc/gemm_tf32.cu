@@ -109,7 +109,7 @@ tf32_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         for (int j = 0; j < BN / 32; ++j) tma_load_2d(sb + j * 4096, &tmB, &full_bar[s], n0 + 32 * j, r0);
       }
     }
-  } else if (warp == 1 && lane == 0) {
+  } else if (warp == 1) {
     // ---------------- MMA issuer (one thread) ----------------
     const uint32_t idesc = (1u << 4)                      // D format  = F32
                            | (2u << 7) | (2u << 10)       // A, B format = TF32

@@ -173,10 +173,21 @@ __device__ __forceinline__ void mbar_wait_addr(uint32_t addr, uint32_t parity) {
 }
 
 // UMMAS = MMAs per k-block (BK / 8 for tf32). Stage layout: [A tile | B tile], stage_bytes apart.
+// Called by ALL 32 lanes of the MMA warp with warp-uniform arguments: the loop state then lives in uniform
+// registers and only the tcgen05 instructions sit behind elect.sync (a `lane == 0` branch around the whole loop
+// makes the compiler rebuild every descriptor through R2UR + an ELECT loop, ~85 cycles per MMA with 12 producer
+// warps competing for issue slots).
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile("{\n\t.reg .pred P;\n\telect.sync _|P, 0xffffffff;\n\tselp.u32 %0, 1, 0, P;\n\t}" : "=r"(pred));
+  return pred != 0;
+}
+
 template <int UMMAS>
 __device__ __forceinline__ void mma_issue_loop(uint32_t tmem_d, uint32_t idesc, uint32_t smem_saddr, uint32_t stage_bytes,
                                                uint32_t a_bytes, OperandDesc a, OperandDesc b, uint32_t full_saddr,
-                                               uint32_t empty_saddr, uint32_t tmem_full_saddr, int stages, int nkb) {
+                                               uint32_t empty_saddr, uint32_t tmem_full_saddr, int stages, int nkb,
+                                               long long* trace = nullptr) {
   const uint32_t a_lo0 = ((smem_saddr & 0x3FFFFu) >> 4) | ((a.lbo >> 4) << 16);
   const uint32_t b_lo0 = (((smem_saddr + a_bytes) & 0x3FFFFu) >> 4) | ((b.lbo >> 4) << 16);
   const uint32_t a_hi = (a.sbo >> 4) | (1u << 14) | (a.layout_type << 29);
@@ -186,21 +197,31 @@ __device__ __forceinline__ void mma_issue_loop(uint32_t tmem_d, uint32_t idesc, 
   int s = 0;
 #pragma unroll 1
   for (int i = 0; i < nkb; ++i) {
+#ifdef B200_CONV_TRACE
+    if (trace && (threadIdx.x & 31) == 0) trace[i * 8 + 3] = clock64();
+#endif
     mbar_wait_addr(fb, ph);
+#ifdef B200_CONV_TRACE
+    if (trace && (threadIdx.x & 31) == 0) trace[i * 8 + 4] = clock64();
+#endif
     tc_fence_after();
+    if (elect_one()) {
 #pragma unroll
-    for (int k = 0; k < UMMAS; ++k) {
-      umma_tf32_lohi(tmem_d, a_lo + k * a_step, a_hi, b_lo + k * b_step, b_hi, idesc, acc);
-      acc = 1u;
+      for (int k = 0; k < UMMAS; ++k) umma_tf32_lohi(tmem_d, a_lo + k * a_step, a_hi, b_lo + k * b_step, b_hi, idesc, k ? 1u : acc);
+      umma_commit_addr(eb);               // frees this smem stage when the MMAs above retire
     }
-    umma_commit_addr(eb);                 // frees this smem stage when the MMAs above retire
+    acc = 1u;
+#ifdef B200_CONV_TRACE
+    if (trace && (threadIdx.x & 31) == 0) trace[i * 8 + 5] = clock64();
+#endif
     if (++s == stages) {
       s = 0; ph ^= 1u; a_lo = a_lo0; b_lo = b_lo0; fb = full_saddr; eb = empty_saddr;
     } else {
       a_lo += stage_step; b_lo += stage_step; fb += 8u; eb += 8u;
     }
   }
-  umma_commit_addr(tmem_full_saddr);      // accumulator complete -> epilogue may read TMEM
+  if (elect_one()) umma_commit_addr(tmem_full_saddr);      // accumulator complete -> epilogue may read TMEM
+  __syncwarp();
 }
 
 }  // namespace tc
