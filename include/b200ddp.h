@@ -136,6 +136,15 @@ int b200ddp_conv2d_wgrad(const float* x, const float* dy, float* dw, const int* 
  * matrices with the reduction index in channel-inner order (k_order 1). */
 int b200ddp_conv2d_weight_prep(const float* w, float* out, int Cout, int Cin, int KH, int KW, long long ld_out, int mode,
                                int device, void* stream);
+/* Several weight_prep jobs in one launch (at most 16): what a training step needs for all conv layers at once. */
+typedef struct b200ddp_weight_prep_job {
+  const float* w;      /* [Cout][Cin][KH][KW] */
+  float* out;
+  int Cout, Cin, KH, KW;
+  long long ld_out;
+  int mode;            /* as b200ddp_conv2d_weight_prep */
+} b200ddp_weight_prep_job;
+int b200ddp_conv2d_weight_prep_multi(const b200ddp_weight_prep_job* jobs, int njobs, int device, void* stream);
 /* out[c] = sum over (n, pix) dy[n][c][pix] — the conv bias gradient. scratch: 256-byte aligned, zeroed once. */
 long long b200ddp_channel_sum_scratch_bytes(int Nb, int C);
 int b200ddp_channel_sum(const float* dy, float* out, int Nb, int C, int HW, void* scratch, long long scratch_bytes,
@@ -157,6 +166,16 @@ int b200ddp_relu_maxpool_fwd(const float* x, float* y, unsigned char* idx, int B
                              int device, void* stream);
 int b200ddp_relu_maxpool_bwd(const float* dy, const unsigned char* idx, float* dx, int B, int C, int H, int W,
                              int device, void* stream);
+/* The same two backward passes, additionally producing the bias gradient of the convolution whose output gradient
+ * they compute (torch: aten::convolution_backward's grad_bias = dY.sum((0,2,3)), reached from reference :125):
+ * db[c] = sum over batch and plane of dx. Per-plane sums in fp64 scratch, folded over the batch in a fixed order by
+ * a second small kernel (deterministic). scratch: b200ddp_bias_grad_scratch_bytes(B, C) bytes, 8-byte aligned, need
+ * not be initialised. relu_bwd_bias: dx = dy * (y > 0) on [B][C][HW], HW <= 4096. */
+long long b200ddp_bias_grad_scratch_bytes(int B, int C);
+int b200ddp_relu_maxpool_bwd_bias(const float* dy, const unsigned char* idx, float* dx, float* db, int B, int C, int H,
+                                  int W, void* scratch, long long scratch_bytes, int device, void* stream);
+int b200ddp_relu_bwd_bias(const float* dy, const float* y, float* dx, float* db, int B, int C, int HW, void* scratch,
+                          long long scratch_bytes, int device, void* stream);
 int b200ddp_relu_fwd(float* x, long long n, int device, void* stream);
 int b200ddp_relu_bwd(const float* dy, const float* y, float* dx, long long n, int device, void* stream);
 int b200ddp_dropout_fwd(const float* x, float* y, unsigned char* gate, long long n, float p, unsigned long long seed,

@@ -135,6 +135,21 @@ for (C, H, tag) in ((64, 55, "pool1"), (192, 27, "pool2"), (256, 13, "pool3")):
                                                    "pf"), 4.0 * xin.numel() + 5.0 * yo.numel())
     timeit(f"relu_maxpool_bwd {tag}", lambda: chk(L.b200ddp_relu_maxpool_bwd(dyo.data_ptr(), idx.data_ptr(), dxi.data_ptr(), B, C, H, H, 0, st()),
                                                    "pb"), 4.0 * xin.numel() + 5.0 * yo.numel())
+    dbo = torch.empty(C, device=DEV)
+    scr = torch.zeros(int(L.b200ddp_bias_grad_scratch_bytes(B, C)), dtype=torch.uint8, device=DEV)
+    timeit(f"relu_maxpool_bwd_bias {tag}", lambda: chk(L.b200ddp_relu_maxpool_bwd_bias(dyo.data_ptr(), idx.data_ptr(), dxi.data_ptr(), dbo.data_ptr(),
+                                                                                        B, C, H, H, scr.data_ptr(), scr.numel(), 0, st()),
+                                                        "pbb"), 4.0 * xin.numel() + 5.0 * yo.numel())
+for (C, tag) in ((384, "conv3"), (256, "conv4")):
+    yr = torch.randn(B, C, 13, 13, device=DEV)
+    gr = torch.randn_like(yr)
+    dxr = torch.empty_like(yr)
+    dbr = torch.empty(C, device=DEV)
+    scr = torch.zeros(int(L.b200ddp_bias_grad_scratch_bytes(B, C)), dtype=torch.uint8, device=DEV)
+    timeit(f"relu_bwd_bias {tag}", lambda: chk(L.b200ddp_relu_bwd_bias(gr.data_ptr(), yr.data_ptr(), dxr.data_ptr(), dbr.data_ptr(), B, C, 169,
+                                                                       scr.data_ptr(), scr.numel(), 0, st()), "rbb"), 12.0 * yr.numel())
+    timeit(f"relu_bwd {tag}", lambda: chk(L.b200ddp_relu_bwd(gr.data_ptr(), yr.data_ptr(), dxr.data_ptr(), yr.numel(), 0, st()), "rb"),
+           12.0 * yr.numel())
 xin = torch.randn(B, 384, 13, 13, device=DEV)
 timeit("relu_fwd conv3", lambda: chk(L.b200ddp_relu_fwd(xin.data_ptr(), xin.numel(), 0, st()), "relu"), 8.0 * xin.numel())
 

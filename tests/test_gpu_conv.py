@@ -89,6 +89,54 @@ def test_conv_full_batch_first_layer_and_relu_backward():
     assert rel_l2 < 2e-2                          # a few ReLU gates flip near zero (TF32 forward)
 
 
+@pytest.mark.parametrize("layer", [0, 1, 4])
+def test_conv_relu_pool_fused_module_matches_float64(layer):
+    """Conv2d(pool=True) = conv -> ReLU -> MaxPool2d(3,2) in one autograd node (the three pooled layers of the toy
+    model); the bias gradient comes out of the pool-backward kernel."""
+    Cin, H, Cout, K, s, p = LAYERS[layer]
+    batch = 6
+    torch.manual_seed(300 + layer)
+    x = torch.randn(batch, Cin, H, H, device=DEV, requires_grad=(layer > 0))
+    conv = bnn.Conv2d(Cin, Cout, K, stride=s, padding=p, pool=True).to(DEV)
+    out = conv(x)
+    x64 = x.detach().double().requires_grad_(layer > 0)
+    w64 = conv.weight.detach().double().requires_grad_()
+    b64 = conv.bias.detach().double().requires_grad_()
+    z64 = torch.nn.functional.conv2d(x64, w64, b64, stride=s, padding=p)
+    o64 = torch.nn.functional.max_pool2d(torch.relu(z64), 3, 2)
+    assert out.shape == o64.shape
+    assert _err(out, o64.detach()) < TOL
+    g = torch.randn_like(out)
+    out.backward(g)
+    o64.backward(g.double())
+
+    def rel_l2(a, b):
+        return float((a.double() - b).norm() / b.norm())
+    # (1) end to end against the float64 network: a TF32 forward picks a different window maximum / ReLU gate where
+    # two candidates are within rounding, so gradients agree in relative L2 only (same bound as the step test)
+    assert rel_l2(conv.weight.grad, w64.grad) < 5e-2
+    assert rel_l2(conv.bias.grad, b64.grad) < 5e-2
+    if layer > 0:
+        assert rel_l2(x.grad, x64.grad) < 5e-2
+    # (2) exactness of the backward kernels given OUR forward's decisions: take the pool / ReLU routing from our own
+    # conv output, do everything else in float64
+    plain = bnn.Conv2d(Cin, Cout, K, stride=s, padding=p).to(DEV)
+    plain.load_state_dict(conv.state_dict())
+    with torch.no_grad():
+        z_ours = plain(x.detach())
+    zl = z_ours.double().requires_grad_()
+    torch.nn.functional.max_pool2d(torch.relu(zl), 3, 2).backward(g.double())
+    dz = zl.grad                                   # gradient of the conv output under our routing
+    x2 = x.detach().double().requires_grad_(layer > 0)
+    w2 = conv.weight.detach().double().requires_grad_()
+    b2 = conv.bias.detach().double().requires_grad_()
+    torch.nn.functional.conv2d(x2, w2, b2, stride=s, padding=p).backward(dz)
+    assert _err(conv.weight.grad, w2.grad) < TOL
+    assert _err(conv.bias.grad, b2.grad) < 1e-5
+    if layer > 0:
+        assert _err(x.grad, x2.grad) < TOL
+
+
 def test_weight_prep_and_channel_sum_exact():
     L = _lib.load()
     st = torch.cuda.current_stream(DEV).cuda_stream

@@ -344,6 +344,48 @@ def test_relu_maxpool_golden_and_alexnet_shapes(golden_dir):
     assert torch.equal(y, yt.detach()) and torch.allclose(dx, xt.grad, rtol=0, atol=1e-6)
 
 
+@pytest.mark.parametrize("shape", [(128, 64, 55, 55), (128, 192, 27, 27), (128, 256, 13, 13), (3, 5, 9, 7)])
+def test_pool_and_relu_backward_with_fused_bias_gradient(shape):
+    """relu_maxpool_bwd_bias / relu_bwd_bias: dx bit-identical to the plain backward kernels, db = dx.sum((0,2,3))
+    (fp64 fold), twice in a row on the same scratch (the ticket must be left at zero)."""
+    B, C, H, W = shape
+    torch.manual_seed(B * C + H)
+    x = torch.randn(B, C, H, W, device=DEV)
+    OH, OW = (H - 3) // 2 + 1, (W - 3) // 2 + 1
+    y = torch.empty(B, C, OH, OW, device=DEV)
+    idx = torch.empty(B, C, OH, OW, dtype=torch.uint8, device=DEV)
+    call("b200ddp_relu_maxpool_fwd", x.data_ptr(), y.data_ptr(), idx.data_ptr(), B, C, H, W, 1, 0, st())
+    nb = int(L().b200ddp_bias_grad_scratch_bytes(B, C))
+    scratch = torch.zeros(nb, dtype=torch.uint8, device=DEV)
+    for rep in range(2):
+        dy = torch.randn(B, C, OH, OW, device=DEV)
+        ref = torch.empty_like(x)
+        call("b200ddp_relu_maxpool_bwd", dy.data_ptr(), idx.data_ptr(), ref.data_ptr(), B, C, H, W, 0, st())
+        dx = torch.empty_like(x)
+        db = torch.empty(C, device=DEV)
+        call("b200ddp_relu_maxpool_bwd_bias", dy.data_ptr(), idx.data_ptr(), dx.data_ptr(), db.data_ptr(), B, C, H, W,
+             scratch.data_ptr(), scratch.numel(), 0, st())
+        assert torch.equal(dx, ref)
+        want = ref.double().sum((0, 2, 3))
+        assert float((db.double() - want).abs().max()) <= 1e-5 * float(want.abs().max()) + 1e-6
+        # ReLU-only variant on the input-sized tensor
+        g = torch.randn_like(x)
+        yr = torch.relu(x)
+        dx2 = torch.empty_like(x)
+        db2 = torch.empty(C, device=DEV)
+        call("b200ddp_relu_bwd_bias", g.data_ptr(), yr.data_ptr(), dx2.data_ptr(), db2.data_ptr(), B, C, H * W,
+             scratch.data_ptr(), scratch.numel(), 0, st())
+        want2 = g * (x > 0)
+        assert torch.equal(dx2, want2)
+        w2 = want2.double().sum((0, 2, 3))
+        assert float((db2.double() - w2).abs().max()) <= 1e-5 * float(w2.abs().max()) + 1e-6
+    # against autograd through relu -> max_pool2d
+    xt = x.clone().requires_grad_()
+    yt = torch.nn.functional.max_pool2d(torch.relu(xt), 3, 2)
+    yt.backward(dy)
+    assert torch.allclose(dx, xt.grad, rtol=0, atol=1e-6)
+
+
 def test_relu_and_dropout_kernels():
     x = torch.randn(1_000_003, device=DEV)
     y = x.clone()

@@ -25,6 +25,12 @@ class B200Error(RuntimeError):
 
 _P = c_void_p  # every device pointer travels as void*
 
+class WeightPrepJob(ctypes.Structure):
+    """b200ddp_weight_prep_job (include/b200ddp.h)."""
+    _fields_ = [("w", c_void_p), ("out", c_void_p), ("Cout", c_int), ("Cin", c_int), ("KH", c_int), ("KW", c_int),
+                ("ld_out", c_longlong), ("mode", c_int)]
+
+
 _PROTOS = {
     "b200ddp_last_error": (c_char_p, []),
     "b200ddp_version": (c_int, []),
@@ -63,12 +69,16 @@ _PROTOS = {
     "b200ddp_conv2d_wgrad": (c_int, [_P, _P, _P, _P, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int,
                                      _P, c_longlong, c_int, _P]),
     "b200ddp_conv2d_weight_prep": (c_int, [_P, _P, c_int, c_int, c_int, c_int, c_longlong, c_int, c_int, _P]),
+    "b200ddp_conv2d_weight_prep_multi": (c_int, [POINTER(WeightPrepJob), c_int, c_int, _P]),
     "b200ddp_channel_sum_scratch_bytes": (c_longlong, [c_int, c_int]),
     "b200ddp_channel_sum": (c_int, [_P, _P, c_int, c_int, c_int, _P, c_longlong, c_int, _P]),
     "b200ddp_channel_sum_static": (c_int, [_P, _P, c_int, c_int, c_int, c_int, _P]),
     "b200ddp_relu_maxpool_fwd": (c_int, [_P, _P, _P, c_int, c_int, c_int, c_int, c_int, c_int, _P]),
     "b200ddp_relu_maxpool_bwd": (c_int, [_P, _P, _P, c_int, c_int, c_int, c_int, c_int, _P]),
     "b200ddp_relu_fwd": (c_int, [_P, c_longlong, c_int, _P]),
+    "b200ddp_bias_grad_scratch_bytes": (c_longlong, [c_int, c_int]),
+    "b200ddp_relu_maxpool_bwd_bias": (c_int, [_P, _P, _P, _P, c_int, c_int, c_int, c_int, _P, c_longlong, c_int, _P]),
+    "b200ddp_relu_bwd_bias": (c_int, [_P, _P, _P, _P, c_int, c_int, c_int, _P, c_longlong, c_int, _P]),
     "b200ddp_relu_bwd": (c_int, [_P, _P, _P, c_longlong, c_int, _P]),
     "b200ddp_dropout_fwd": (c_int, [_P, _P, _P, c_longlong, c_float, c_ulonglong, c_int, _P]),
     "b200ddp_bn_scratch_bytes": (c_longlong, [c_int, c_int]),

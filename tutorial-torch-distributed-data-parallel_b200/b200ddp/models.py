@@ -34,16 +34,16 @@ class AlexNet(nn.Module):
             raise ValueError("conv must be 'b200' (own implicit-GEMM kernels) or 'cudnn' (torch.nn.Conv2d)")
         if not bn and conv == "b200":
             self.features = nn.Sequential(
-                bnn.Conv2d(3, 64, kernel_size=11, stride=4, padding=2),
-                bnn.ReLUMaxPool2d(), nn.Identity(),
-                bnn.Conv2d(64, 192, kernel_size=5, padding=2),
-                bnn.ReLUMaxPool2d(), nn.Identity(),
+                bnn.Conv2d(3, 64, kernel_size=11, stride=4, padding=2, pool=True),
+                nn.Identity(), nn.Identity(),
+                bnn.Conv2d(64, 192, kernel_size=5, padding=2, pool=True),
+                nn.Identity(), nn.Identity(),
                 bnn.Conv2d(192, 384, kernel_size=3, padding=1, relu=True),
                 nn.Identity(),
                 bnn.Conv2d(384, 256, kernel_size=3, padding=1, relu=True),
                 nn.Identity(),
-                bnn.Conv2d(256, 256, kernel_size=3, padding=1),
-                bnn.ReLUMaxPool2d(), nn.Identity(),
+                bnn.Conv2d(256, 256, kernel_size=3, padding=1, pool=True),
+                nn.Identity(), nn.Identity(),
             )
         elif not bn:
             self.features = nn.Sequential(
@@ -77,6 +77,9 @@ class AlexNet(nn.Module):
         )
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
+        convs = [m for m in self.features if isinstance(m, bnn.Conv2d)]
+        if convs and x.is_cuda:
+            bnn.prepare_conv_weights(convs, first_needs_dgrad=x.requires_grad)     # all GEMM weight copies, one launch
         x = self.features(x)
         if x.shape[-2:] != (6, 6):
             x = self.avgpool(x)

@@ -202,8 +202,12 @@ def conv_weight_matrix(w, mode: int):
 
 
 class _Conv2dFn(torch.autograd.Function):
+    """conv (+bias) [+ReLU in the epilogue] [+ReLU + 3x3/2 max pool]. Backward: the pool / ReLU backward kernel also
+    produces the bias gradient (sum of the conv output gradient over batch and plane), then wgrad and dgrad."""
+
     @staticmethod
-    def forward(ctx, x, weight, bias, stride, pad, relu):
+    def forward(ctx, x, weight, bias, stride, pad, relu, pool, prepared):
+        L = _lib.load()
         x = _lib.f32c(x, "input")
         w = _lib.f32c(weight, "weight")
         Cout, Cin, KH, KW = w.shape
@@ -211,36 +215,70 @@ class _Conv2dFn(torch.autograd.Function):
             raise ValueError(f"Conv2d: input has {x.shape[1]} channels, weight expects {Cin}")
         K = Cin * KH * KW
         ko = _k_order(Cin)
-        if ko == 1:
+        ctx.dgrad_weights = None
+        if prepared is not None:      # GEMM copies made by prepare_conv_weights() for this forward/backward pair
+            wmat, ldw = prepared["fwd"]
+            ctx.dgrad_weights = prepared.get("dgrad")
+        elif ko == 1:
             wmat, ldw = conv_weight_matrix(w, 2)
         elif K % 4 == 0 and w.data_ptr() % 16 == 0:
             wmat, ldw = w, K
         else:   # TMA needs 16-byte aligned rows: zero-padded copy (conv1: K = 363)
             wmat, ldw = conv_weight_matrix(w, 0)
-        y = conv2d_forward_raw(x, wmat, ldw, bias, Cout, KH, KW, stride, pad, relu, ko)
-        ctx.save_for_backward(x, w, y if relu else None)
-        ctx.stride, ctx.pad, ctx.relu = stride, pad, relu
+        y = conv2d_forward_raw(x, wmat, ldw, bias, Cout, KH, KW, stride, pad, relu and not pool, ko)
+        ctx.stride, ctx.pad, ctx.relu, ctx.pool = stride, pad, relu, pool
         ctx.weight_param, ctx.bias_param = weight, bias
+        if pool:
+            B, C, H, W = y.shape
+            if H < 3 or W < 3:
+                raise ValueError("Conv2d(pool=True): the convolution output is smaller than the 3x3 pooling window")
+            OH, OW = (H - 3) // 2 + 1, (W - 3) // 2 + 1
+            out = torch.empty((B, C, OH, OW), dtype=torch.float32, device=x.device)
+            idx = torch.empty((B, C, OH, OW), dtype=torch.uint8, device=x.device)
+            _lib.check(L.b200ddp_relu_maxpool_fwd(y.data_ptr(), out.data_ptr(), idx.data_ptr(), B, C, H, W, int(relu),
+                                                  _lib.dev_index(x), _lib.cur_stream(x.device)), "relu_maxpool_fwd")
+            ctx.save_for_backward(x, w, idx)
+            return out
+        ctx.save_for_backward(x, w, y if relu else None)
         return y
 
     @staticmethod
     def backward(ctx, dy):
         L = _lib.load()
-        x, w, y_relu = ctx.saved_tensors
+        x, w, aux = ctx.saved_tensors
         dev, st = _lib.dev_index(x), _lib.cur_stream(x.device)
         N, Cin, H, W = x.shape
         Cout, _, KH, KW = w.shape
         stride, pad = ctx.stride, ctx.pad
         OH, OW = (H + 2 * pad - KH) // stride + 1, (W + 2 * pad - KW) // stride + 1
         dy = _lib.f32c(dy, "grad_output")
-        if y_relu is not None:
+        want_db = ctx.bias_param is not None and ctx.needs_input_grad[2]
+        db = _grad_target(ctx.bias_param, (Cout,), x.device) if want_db else None
+        have_db = False
+        if want_db and (ctx.pool or ctx.relu):
+            nb = int(L.b200ddp_bias_grad_scratch_bytes(N, Cout))
+            scratch = _lib.workspace(x.device, nb, "bias_grad")
+        if ctx.pool:
+            dz = torch.empty((N, Cout, OH, OW), dtype=torch.float32, device=x.device)
+            if want_db:
+                _lib.check(L.b200ddp_relu_maxpool_bwd_bias(dy.data_ptr(), aux.data_ptr(), dz.data_ptr(), db.data_ptr(), N,
+                                                           Cout, OH, OW, scratch.data_ptr(), scratch.numel(), dev, st),
+                           "relu_maxpool_bwd_bias")
+                have_db = True
+            else:
+                _lib.check(L.b200ddp_relu_maxpool_bwd(dy.data_ptr(), aux.data_ptr(), dz.data_ptr(), N, Cout, OH, OW, dev,
+                                                      st), "relu_maxpool_bwd")
+        elif ctx.relu:
             dz = torch.empty_like(dy)
-            _lib.check(L.b200ddp_relu_bwd(dy.data_ptr(), y_relu.data_ptr(), dz.data_ptr(), dy.numel(), dev, st), "relu_bwd")
+            if want_db and OH * OW <= 4096:
+                _lib.check(L.b200ddp_relu_bwd_bias(dy.data_ptr(), aux.data_ptr(), dz.data_ptr(), db.data_ptr(), N, Cout,
+                                                   OH * OW, scratch.data_ptr(), scratch.numel(), dev, st), "relu_bwd_bias")
+                have_db = True
+            else:
+                _lib.check(L.b200ddp_relu_bwd(dy.data_ptr(), aux.data_ptr(), dz.data_ptr(), dy.numel(), dev, st), "relu_bwd")
         else:
             dz = dy
-        db = None
-        if ctx.bias_param is not None and ctx.needs_input_grad[2]:
-            db = _grad_target(ctx.bias_param, (Cout,), x.device)
+        if want_db and not have_db:
             nb = int(L.b200ddp_channel_sum_scratch_bytes(N, Cout))
             scratch = _lib.workspace(x.device, nb, "chsum", zero=True)
             _lib.check(L.b200ddp_channel_sum(dz.data_ptr(), db.data_ptr(), N, Cout, OH * OW, scratch.data_ptr(),
@@ -261,24 +299,90 @@ class _Conv2dFn(torch.autograd.Function):
                 raise NotImplementedError("b200ddp Conv2d: input gradients are implemented for stride 1 only "
                                           "(the toy model's strided conv is its first layer)")
             ko = _k_order(Cout)          # dgrad reduces over (co, kh', kw')
-            wt, ldt = conv_weight_matrix(w, 3 if ko == 1 else 1)
+            if ctx.dgrad_weights is not None:
+                wt, ldt = ctx.dgrad_weights
+            else:
+                wt, ldt = conv_weight_matrix(w, 3 if ko == 1 else 1)
             dx = conv2d_forward_raw(dz, wt, ldt, None, Cin, KH, KW, 1, KH - 1 - pad, False, ko)
-        return dx, dw, db, None, None, None
+        return dx, dw, db, None, None, None, None, None
 
 
 class Conv2d(nn.Conv2d):
-    """nn.Conv2d (square stride / padding, no dilation / groups) with the following ReLU optionally folded in."""
+    """nn.Conv2d (square stride / padding, no dilation / groups) with the following ReLU (`relu=True`) or the
+    following ReLU + MaxPool2d(3, 2) (`pool=True`, alexnet.py:22-24) optionally folded in."""
 
-    def __init__(self, in_channels, out_channels, kernel_size, stride=1, padding=0, bias=True, relu=False, device=None,
-                 dtype=None) -> None:
+    def __init__(self, in_channels, out_channels, kernel_size, stride=1, padding=0, bias=True, relu=False, pool=False,
+                 device=None, dtype=None) -> None:
         super().__init__(in_channels, out_channels, kernel_size, stride=stride, padding=padding, bias=bias,
                          device=device, dtype=dtype)
         if self.stride[0] != self.stride[1] or self.padding[0] != self.padding[1]:
             raise ValueError("b200ddp Conv2d needs equal stride / padding in both dimensions")
-        self.relu = bool(relu)
+        self.pool = bool(pool)
+        self.relu = bool(relu) or self.pool       # the pooled form always includes the ReLU in front of the pool
+        self._prepared = None                     # set by prepare_conv_weights(), consumed by the next forward
+        self._prep_bufs = {}
+
+    def _prep_jobs(self, need_dgrad: bool):
+        """(jobs, prepared) for prepare_conv_weights: GEMM copies of the weights for forward and, optionally, dgrad."""
+        w = self.weight.data
+        Cout, Cin, KH, KW = w.shape
+        K = Cin * KH * KW
+        jobs, prepared = [], {}
+
+        def buf(tag, rows, ld):
+            t = self._prep_bufs.get(tag)
+            if t is None or t.shape != (rows, ld) or t.device != w.device:
+                t = torch.empty((rows, ld), dtype=torch.float32, device=w.device)
+                self._prep_bufs[tag] = t
+            return t
+        if _k_order(Cin) == 1:
+            out = buf("fwd", Cout, K)
+            jobs.append((w, out, 2, K))
+            prepared["fwd"] = (out, K)
+        elif K % 4 == 0 and w.data_ptr() % 16 == 0:
+            prepared["fwd"] = (w, K)
+        else:
+            ld = (K + 31) // 32 * 32
+            out = buf("fwd", Cout, ld)
+            jobs.append((w, out, 0, ld))
+            prepared["fwd"] = (out, ld)
+        if need_dgrad and self.stride[0] == 1:
+            ld = Cout * KH * KW
+            out = buf("dgrad", Cin, ld)
+            jobs.append((w, out, 3 if _k_order(Cout) == 1 else 1, ld))
+            prepared["dgrad"] = (out, ld)
+        return jobs, prepared
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
-        return _Conv2dFn.apply(x, self.weight, self.bias, self.stride[0], self.padding[0], self.relu)
+        prepared, self._prepared = self._prepared, None
+        return _Conv2dFn.apply(x, self.weight, self.bias, self.stride[0], self.padding[0], self.relu, self.pool, prepared)
+
+
+def prepare_conv_weights(convs, first_needs_dgrad: bool = False) -> None:
+    """One launch (b200ddp_conv2d_weight_prep_multi) that writes the GEMM copies of the weights of every Conv2d in
+    `convs` (in network order) for the forward pass that follows and its backward: forward copies for all layers,
+    dgrad copies for all but the first (whose input needs no gradient unless `first_needs_dgrad`)."""
+    L = _lib.load()
+    convs = list(convs)
+    if not convs:
+        return
+    jobs = []
+    for i, conv in enumerate(convs):
+        if not conv.weight.is_cuda or conv.weight.dtype != torch.float32 or not conv.weight.is_contiguous():
+            conv._prepared = None
+            continue
+        j, prepared = conv._prep_jobs(need_dgrad=(i > 0 or first_needs_dgrad))
+        jobs += j
+        conv._prepared = prepared
+    dev = convs[0].weight.device
+    for k in range(0, len(jobs), 16):
+        part = jobs[k:k + 16]
+        arr = (_lib.WeightPrepJob * len(part))()
+        for a, (w, out, mode, ld) in zip(arr, part):
+            Cout, Cin, KH, KW = w.shape
+            a.w, a.out, a.Cout, a.Cin, a.KH, a.KW, a.ld_out, a.mode = w.data_ptr(), out.data_ptr(), Cout, Cin, KH, KW, ld, mode
+        _lib.check(L.b200ddp_conv2d_weight_prep_multi(arr, len(part), dev.index or 0, _lib.cur_stream(dev)),
+                   "conv2d_weight_prep_multi")
 
 
 # ---------------------------------------------------------------------------------------------------------

@@ -503,20 +503,20 @@ __global__ void __launch_bounds__(256) wgrad_finalize_ci_kernel(const float* __r
 // mode 1: dgrad weights, k' = (co, kh', kw'):  out[ci][co*KH*KW + (KH-1-kh)*KW + (KW-1-kw)] = w[co][ci][kh][kw]
 // mode 2: forward weights in channel-inner order:  out[co][(kh*KW + kw)*Cin + ci]             = w[co][ci][kh][kw]
 // mode 3: dgrad weights in channel-inner order:    out[ci][((KH-1-kh)*KW + (KW-1-kw))*Cout + co] = w[co][ci][kh][kw]
-__global__ void __launch_bounds__(256) conv_weight_prep_kernel(const float* __restrict__ w, float* __restrict__ out,
-                                                               int Cout, int Cin, int KH, int KW, long long ld_out,
-                                                               int mode) {
+__device__ __forceinline__ void weight_prep_body(const float* __restrict__ w, float* __restrict__ out, int Cout, int Cin,
+                                                 int KH, int KW, long long ld_out, int mode, long long first,
+                                                 long long stride) {
   const int KHW = KH * KW;
   if (mode == 0) {
     const int K = Cin * KHW;
-    const long long total = (long long)Cout * ld_out, stride = (long long)gridDim.x * blockDim.x;
-    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
+    const long long total = (long long)Cout * ld_out;
+    for (long long i = first; i < total; i += stride) {
       const int co = (int)(i / ld_out), k = (int)(i - (long long)co * ld_out);
       out[i] = k < K ? __ldg(w + (long long)co * K + k) : 0.f;
     }
   } else if (mode == 2 || mode == 3) {
-    const long long total = (long long)Cout * Cin * KHW, stride = (long long)gridDim.x * blockDim.x;
-    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
+    const long long total = (long long)Cout * Cin * KHW;
+    for (long long i = first; i < total; i += stride) {
       // i enumerates the INPUT w[co][ci][kh][kw]
       const int kw = (int)(i % KW);
       long long t = i / KW;
@@ -528,8 +528,8 @@ __global__ void __launch_bounds__(256) conv_weight_prep_kernel(const float* __re
       else out[(long long)ci * ld_out + (long long)((KH - 1 - kh) * KW + (KW - 1 - kw)) * Cout + co] = v;
     }
   } else {
-    const long long total = (long long)Cout * Cin * KHW, stride = (long long)gridDim.x * blockDim.x;
-    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
+    const long long total = (long long)Cout * Cin * KHW;
+    for (long long i = first; i < total; i += stride) {
       // i enumerates the OUTPUT: [ci][co][kh'][kw']
       const int kwp = (int)(i % KW);
       long long t = i / KW;
@@ -540,6 +540,31 @@ __global__ void __launch_bounds__(256) conv_weight_prep_kernel(const float* __re
       out[(long long)ci * ld_out + (long long)co * KHW + khp * KW + kwp] = __ldg(w + src);
     }
   }
+}
+
+__global__ void __launch_bounds__(256) conv_weight_prep_kernel(const float* __restrict__ w, float* __restrict__ out,
+                                                               int Cout, int Cin, int KH, int KW, long long ld_out,
+                                                               int mode) {
+  weight_prep_body(w, out, Cout, Cin, KH, KW, ld_out, mode, (long long)blockIdx.x * blockDim.x + threadIdx.x,
+                   (long long)gridDim.x * blockDim.x);
+}
+
+// All weight copies of a step in ONE launch (the toy model needs 9: five forward, four dgrad): job j owns the
+// CTAs [first_block[j], first_block[j+1]).
+constexpr int kMaxPrepJobs = 16;
+struct PrepJobs {
+  b200ddp_weight_prep_job job[kMaxPrepJobs];
+  int first_block[kMaxPrepJobs + 1];
+  int n;
+};
+__global__ void __launch_bounds__(256) conv_weight_prep_multi_kernel(const __grid_constant__ PrepJobs J) {
+  int j = 0;
+  while (j + 1 < J.n && (int)blockIdx.x >= J.first_block[j + 1]) ++j;
+  const b200ddp_weight_prep_job& q = J.job[j];
+  const int nblocks = J.first_block[j + 1] - J.first_block[j];
+  weight_prep_body(q.w, q.out, q.Cout, q.Cin, q.KH, q.KW, q.ld_out, q.mode,
+                   (long long)((int)blockIdx.x - J.first_block[j]) * blockDim.x + threadIdx.x,
+                   (long long)nblocks * blockDim.x);
 }
 
 // out[c] = sum over (n, pix) of dy[n][c][pix]  (bias gradient). S x C CTAs, deterministic last-ticket merge.
@@ -806,6 +831,33 @@ int b200ddp_conv2d_weight_prep(const float* w, float* out, int Cout, int Cin, in
   long long want = (total + 255) / 256;
   const int grid = (int)(want < kNumSMs * 8 ? (want < 1 ? 1 : want) : kNumSMs * 8);
   conv_weight_prep_kernel<<<grid, 256, 0, as_stream(stream)>>>(w, out, Cout, Cin, KH, KW, ld_out, mode);
+  B200_LAUNCH_OK();
+  return 0;
+}
+
+int b200ddp_conv2d_weight_prep_multi(const b200ddp_weight_prep_job* jobs, int njobs, int device, void* stream) {
+  B200_CHECK_ARG(jobs && njobs > 0 && njobs <= kMaxPrepJobs, "conv2d_weight_prep_multi: 1..%d jobs (got %d)", kMaxPrepJobs, njobs);
+  PrepJobs J;
+  J.n = njobs;
+  int blocks = 0;
+  for (int j = 0; j < njobs; ++j) {
+    const b200ddp_weight_prep_job& q = jobs[j];
+    B200_CHECK_ARG(q.w && q.out && q.Cout > 0 && q.Cin > 0 && q.KH > 0 && q.KW > 0, "conv2d_weight_prep_multi: job %d: bad argument", j);
+    B200_CHECK_ARG(q.mode >= 0 && q.mode <= 3, "conv2d_weight_prep_multi: job %d: mode must be 0..3", j);
+    B200_CHECK_ARG((q.mode == 0 || q.mode == 2) ? q.ld_out >= (long long)q.Cin * q.KH * q.KW
+                                                : q.ld_out >= (long long)q.Cout * q.KH * q.KW,
+                   "conv2d_weight_prep_multi: job %d: ld_out too small", j);
+    const long long total = q.mode == 0 ? (long long)q.Cout * q.ld_out : (long long)q.Cout * q.Cin * q.KH * q.KW;
+    long long want = (total + 1023) / 1024;                      // ~4 elements per thread
+    if (want < 1) want = 1;
+    if (want > kNumSMs * 4) want = kNumSMs * 4;
+    J.job[j] = q;
+    J.first_block[j] = blocks;
+    blocks += (int)want;
+  }
+  J.first_block[njobs] = blocks;
+  B200_DEVICE(device);
+  conv_weight_prep_multi_kernel<<<blocks, 256, 0, as_stream(stream)>>>(J);
   B200_LAUNCH_OK();
   return 0;
 }

@@ -42,41 +42,128 @@ __global__ void __launch_bounds__(256) relu_maxpool_fwd_kernel(const float* __re
 }
 
 // dx[b,c,h,w] = sum over the (<= 4) windows that cover (h,w) and selected it of dy[window].
-// One CTA per (b,c) plane: the plane's dy and argmax codes (<= 27x27) are staged in shared memory, then
-// every input pixel gathers from them (deterministic, no atomics). 32-bit index math only.
-constexpr int kPoolMaxOut = 27 * 27;
+// Backward of ReLU + 3x3/2 max pool, optionally with the bias gradient of the convolution that fed it.
+// A CTA stages the dy and argmax codes of P whole planes (<= kPoolChunk pooled elements, contiguous in NCHW) in
+// shared memory and then produces the P input planes as one contiguous, coalesced stream: every input pixel
+// gathers from the <= 2x2 windows that contain it (deterministic, no atomics). With `plane_sums` the CTA also
+// writes sum(dx) of each plane - which is just the sum of the open dy entries - and bias_fold_kernel adds them over
+// the batch in a fixed order into db[c] (fp64 accumulation): the five channel_sum passes over the conv outputs'
+// gradients disappear from the step.
+constexpr int kPoolChunk = 2048;
+
+// db[c] = sum_b plane_sums[b][c] in fp64, fixed order: one warp per channel, lane l adds b = l, l+32, ... and the
+// 32 partials are combined by a shuffle tree. A separate small launch: folding inside the producing kernel by its
+// last CTA (ticket) was measured at 13-60 us of single-SM tail per layer, this costs 3-4 us.
+__global__ void __launch_bounds__(256) bias_fold_kernel(const double* __restrict__ plane_sums, float* __restrict__ db,
+                                                        int B, int C) {
+  const int c = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+  if (c >= C) return;
+  double s = 0.0;
+  for (int bI = lane; bI < B; bI += 32) s += __ldcg(plane_sums + (long long)bI * C + c);
+#pragma unroll
+  for (int sft = 16; sft > 0; sft >>= 1) s += __shfl_xor_sync(0xffffffffu, s, sft);
+  if (lane == 0) db[c] = (float)s;
+}
+
 __global__ void __launch_bounds__(256) relu_maxpool_bwd_kernel(const float* __restrict__ dy,
                                                                const unsigned char* __restrict__ idx,
-                                                               float* __restrict__ dx, long long planes, int H, int W,
-                                                               int OH, int OW) {
-  __shared__ float s_dy[kPoolMaxOut];
-  __shared__ unsigned char s_idx[kPoolMaxOut];
+                                                               float* __restrict__ dx, double* __restrict__ plane_sums,
+                                                               int B, int C, int H, int W, int OH, int OW, int P) {
+  __shared__ float s_dy[kPoolChunk];
+  __shared__ unsigned char s_idx[kPoolChunk];
   const int ohw = OH * OW, hw = H * W;
-  for (long long pl = blockIdx.x; pl < planes; pl += gridDim.x) {
-    const float* dyp = dy + pl * ohw;
-    const unsigned char* ip = idx + pl * ohw;
-    for (int i = threadIdx.x; i < ohw; i += blockDim.x) {
+  const long long planes = (long long)B * C;
+  const long long nchunks = (planes + P - 1) / P;
+  const int QH = (H + 1) >> 1, QW = (W + 1) >> 1, qhw = QH * QW;
+  const float inv_qhw = 1.0f / (float)qhw, inv_qw = 1.0f / (float)QW;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
+  for (long long chunk = blockIdx.x; chunk < nchunks; chunk += gridDim.x) {
+    const long long pl0 = chunk * P;
+    const int np = (int)(planes - pl0 < P ? planes - pl0 : P);
+    const int n_in = np * ohw;
+    const float* dyp = dy + pl0 * ohw;
+    const unsigned char* ip = idx + pl0 * ohw;
+    for (int i = threadIdx.x; i < n_in; i += blockDim.x) {
       s_dy[i] = __ldg(dyp + i);
       s_idx[i] = __ldg(ip + i);
     }
     __syncthreads();
-    float* dxp = dx + pl * hw;
-    // warp <-> input row, lane <-> column: no integer division, straight-line window tests. A pixel (h,w) lies
-    // in window rows {h>>1} and, when h is even, {(h>>1)-1} (same for columns): at most 2x2 candidates.
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
-    for (int h = warp; h < H; h += nwarps) {
-      const int oh1 = h >> 1, oh0 = oh1 - 1, hodd = h & 1;
-      const bool vh1 = oh1 < OH, vh0 = !hodd && oh0 >= 0;
-      for (int w = lane; w < W; w += 32) {
-        const int ow1 = w >> 1, ow0 = ow1 - 1, wodd = w & 1;
-        const bool vw1 = ow1 < OW, vw0 = !wodd && ow0 >= 0;
-        float g = 0.f;
-        if (vh1 && vw1) { const int o = oh1 * OW + ow1; if ((int)s_idx[o] == hodd * 3 + wodd) g += s_dy[o]; }
-        if (vh1 && vw0) { const int o = oh1 * OW + ow0; if ((int)s_idx[o] == hodd * 3 + 2) g += s_dy[o]; }
-        if (vh0 && vw1) { const int o = oh0 * OW + ow1; if ((int)s_idx[o] == 6 + wodd) g += s_dy[o]; }
-        if (vh0 && vw0) { const int o = oh0 * OW + ow0; if ((int)s_idx[o] == 8) g += s_dy[o]; }
-        dxp[h * W + w] = g;
+    if (plane_sums) {
+      for (int pl = warp; pl < np; pl += nwarps) {
+        float acc = 0.f;
+        for (int o = lane; o < ohw; o += 32) acc += s_idx[pl * ohw + o] != 255 ? s_dy[pl * ohw + o] : 0.f;
+        double d = (double)acc;
+#pragma unroll
+        for (int sft = 16; sft > 0; sft >>= 1) d += __shfl_xor_sync(0xffffffffu, d, sft);
+        if (lane == 0) plane_sums[pl0 + pl] = d;
       }
+    }
+    // One thread per 2x2 input quad (rows 2a, 2a+1; columns 2b, 2b+1). Window (a,b) covers the whole quad (slots
+    // 0,1,3,4), window (a,b-1) its left column (slots 2,5), window (a-1,b) its top row (slots 6,7) and window
+    // (a-1,b-1) the top-left pixel (slot 8): four (dy, slot) pairs from shared memory, nine compares, four stores.
+    float* dxp = dx + pl0 * hw;
+    const int n_quads = np * qhw;
+    for (int i = threadIdx.x; i < n_quads; i += blockDim.x) {
+      int pl = (int)(((float)i + 0.5f) * inv_qhw), rem = i - pl * qhw;      // exact: i < 2^23, see conv.cu
+      if (rem < 0) { --pl; rem += qhw; } else if (rem >= qhw) { ++pl; rem -= qhw; }
+      int a = (int)(((float)rem + 0.5f) * inv_qw), bq = rem - a * QW;
+      if (bq < 0) { --a; bq += QW; } else if (bq >= QW) { ++a; bq -= QW; }
+      const float* sd = s_dy + pl * ohw;
+      const unsigned char* si = s_idx + pl * ohw;
+      const bool va = a < OH, vb = bq < OW, va0 = a > 0, vb0 = bq > 0;
+      float d11 = 0.f, d10 = 0.f, d01 = 0.f, d00 = 0.f;
+      int c11 = 255, c10 = 255, c01 = 255, c00 = 255;
+      if (va && vb) { d11 = sd[a * OW + bq]; c11 = si[a * OW + bq]; }
+      if (va && vb0) { d10 = sd[a * OW + bq - 1]; c10 = si[a * OW + bq - 1]; }
+      if (va0 && vb) { d01 = sd[(a - 1) * OW + bq]; c01 = si[(a - 1) * OW + bq]; }
+      if (va0 && vb0) { d00 = sd[(a - 1) * OW + bq - 1]; c00 = si[(a - 1) * OW + bq - 1]; }
+      const float g00 = (c11 == 0 ? d11 : 0.f) + (c10 == 2 ? d10 : 0.f) + (c01 == 6 ? d01 : 0.f) + (c00 == 8 ? d00 : 0.f);
+      const float g01 = (c11 == 1 ? d11 : 0.f) + (c01 == 7 ? d01 : 0.f);
+      const float g10 = (c11 == 3 ? d11 : 0.f) + (c10 == 5 ? d10 : 0.f);
+      const float g11 = (c11 == 4 ? d11 : 0.f);
+      const int h = 2 * a, w = 2 * bq;
+      float* o = dxp + pl * hw + h * W + w;
+      const bool w1 = w + 1 < W, h1 = h + 1 < H;
+      o[0] = g00;
+      if (w1) o[1] = g01;
+      if (h1) { o[W] = g10; if (w1) o[W + 1] = g11; }
+    }
+    __syncthreads();
+  }
+}
+
+// dx = dy * (y > 0) for [B][C][HW] tensors plus the per-plane sums of dx, folded into db[c] by bias_fold_kernel (the
+// bias gradient of a convolution whose ReLU is fused into its epilogue). A CTA takes P whole planes (contiguous,
+// <= kReluChunk elements): a flat, coalesced elementwise pass that also parks dx in shared memory, then one warp
+// per plane adds its plane up from there.
+constexpr int kReluChunk = 4096;
+__global__ void __launch_bounds__(256) relu_bwd_bias_kernel(const float* __restrict__ dy, const float* __restrict__ y,
+                                                            float* __restrict__ dx, double* __restrict__ plane_sums,
+                                                            int B, int C, int HW, int P) {
+  __shared__ float s_v[kReluChunk];
+  const long long planes = (long long)B * C;
+  const long long nchunks = (planes + P - 1) / P;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
+  for (long long chunk = blockIdx.x; chunk < nchunks; chunk += gridDim.x) {
+    const long long pl0 = chunk * P;
+    const int np = (int)(planes - pl0 < P ? planes - pl0 : P);
+    const int n = np * HW;
+    const long long base = pl0 * HW;
+#pragma unroll 4
+    for (int i = threadIdx.x; i < n; i += blockDim.x) {
+      const float yv = __ldg(y + base + i), gv = __ldg(dy + base + i);     // both loads issued before the select
+      const float v = yv > 0.f ? gv : 0.f;
+      dx[base + i] = v;
+      s_v[i] = v;
+    }
+    __syncthreads();
+    for (int pl = warp; pl < np; pl += nwarps) {
+      float acc = 0.f;
+      for (int o = lane; o < HW; o += 32) acc += s_v[pl * HW + o];
+      double d = (double)acc;
+#pragma unroll
+      for (int sft = 16; sft > 0; sft >>= 1) d += __shfl_xor_sync(0xffffffffu, d, sft);
+      if (lane == 0) plane_sums[pl0 + pl] = d;
     }
     __syncthreads();
   }
@@ -144,15 +231,60 @@ int b200ddp_relu_maxpool_fwd(const float* x, float* y, unsigned char* idx, int B
   return 0;
 }
 
+static int pool_bwd_launch(const float* dy, const unsigned char* idx, float* dx, float* db, int B, int C, int H, int W,
+                           void* scratch, long long scratch_bytes, int device, void* stream, const char* who) {
+  B200_CHECK_ARG(dy && idx && dx && B > 0 && C > 0 && H >= 3 && W >= 3, "%s: bad argument", who);
+  const int OH = (H - kPoolK) / kPoolS + 1, OW = (W - kPoolK) / kPoolS + 1;
+  B200_CHECK_ARG(OH * OW <= kPoolChunk, "%s: pooled plane %dx%d exceeds %d elements", who, OH, OW, kPoolChunk);
+  int P = kPoolChunk / (OH * OW);
+  while (P > 1 && (long long)P * H * W >= (1 << 22)) --P;      // keeps the float-reciprocal index split exact
+  B200_CHECK_ARG((long long)P * H * W < (1 << 23), "%s: plane %dx%d too large", who, H, W);
+  double* plane_sums = nullptr;
+  if (db) {
+    B200_CHECK_ARG(scratch && ((uintptr_t)scratch & 7) == 0 && scratch_bytes >= (long long)B * C * 8,
+                   "%s: scratch too small or unaligned (need %lld bytes, 8-byte aligned)", who, (long long)B * C * 8);
+    plane_sums = reinterpret_cast<double*>(scratch);
+  }
+  B200_DEVICE(device);
+  const long long planes = (long long)B * C, nchunks = (planes + P - 1) / P;
+  const int grid = (int)(nchunks < (long long)kNumSMs * 8 ? nchunks : (long long)kNumSMs * 8);
+  relu_maxpool_bwd_kernel<<<grid, 256, 0, as_stream(stream)>>>(dy, idx, dx, plane_sums, B, C, H, W, OH, OW, P);
+  B200_LAUNCH_OK();
+  if (db) {
+    bias_fold_kernel<<<(C + 7) / 8, 256, 0, as_stream(stream)>>>(plane_sums, db, B, C);
+    B200_LAUNCH_OK();
+  }
+  return 0;
+}
+
 int b200ddp_relu_maxpool_bwd(const float* dy, const unsigned char* idx, float* dx, int B, int C, int H, int W,
                              int device, void* stream) {
-  B200_CHECK_ARG(dy && idx && dx && B > 0 && C > 0 && H >= 3 && W >= 3, "relu_maxpool_bwd: bad argument");
+  return pool_bwd_launch(dy, idx, dx, nullptr, B, C, H, W, nullptr, 0, device, stream, "relu_maxpool_bwd");
+}
+
+long long b200ddp_bias_grad_scratch_bytes(int B, int C) { return (long long)B * C * 8; }
+
+int b200ddp_relu_maxpool_bwd_bias(const float* dy, const unsigned char* idx, float* dx, float* db, int B, int C, int H,
+                                  int W, void* scratch, long long scratch_bytes, int device, void* stream) {
+  B200_CHECK_ARG(db, "relu_maxpool_bwd_bias: db is null (use relu_maxpool_bwd)");
+  return pool_bwd_launch(dy, idx, dx, db, B, C, H, W, scratch, scratch_bytes, device, stream, "relu_maxpool_bwd_bias");
+}
+
+int b200ddp_relu_bwd_bias(const float* dy, const float* y, float* dx, float* db, int B, int C, int HW, void* scratch,
+                          long long scratch_bytes, int device, void* stream) {
+  B200_CHECK_ARG(dy && y && dx && db && B > 0 && C > 0 && HW > 0, "relu_bwd_bias: bad argument");
+  B200_CHECK_ARG(HW <= kReluChunk, "relu_bwd_bias: plane of %d elements exceeds %d", HW, kReluChunk);
+  B200_CHECK_ARG(scratch && ((uintptr_t)scratch & 7) == 0 && scratch_bytes >= (long long)B * C * 8,
+                 "relu_bwd_bias: scratch too small or unaligned (need %lld bytes, 8-byte aligned)", (long long)B * C * 8);
   B200_DEVICE(device);
-  const int OH = (H - kPoolK) / kPoolS + 1, OW = (W - kPoolK) / kPoolS + 1;
   const long long planes = (long long)B * C;
-  B200_CHECK_ARG(OH * OW <= kPoolMaxOut, "relu_maxpool_bwd: pooled plane %dx%d exceeds %d elements", OH, OW, kPoolMaxOut);
-  const int grid = (int)(planes < (long long)kNumSMs * 16 ? planes : (long long)kNumSMs * 16);
-  relu_maxpool_bwd_kernel<<<grid, 256, 0, as_stream(stream)>>>(dy, idx, dx, planes, H, W, OH, OW);
+  const int P = kReluChunk / HW;
+  const long long want = (planes + P - 1) / P;
+  const int grid = (int)(want < (long long)kNumSMs * 8 ? want : (long long)kNumSMs * 8);
+  double* plane_sums = reinterpret_cast<double*>(scratch);
+  relu_bwd_bias_kernel<<<grid, 256, 0, as_stream(stream)>>>(dy, y, dx, plane_sums, B, C, HW, P);
+  B200_LAUNCH_OK();
+  bias_fold_kernel<<<(C + 7) / 8, 256, 0, as_stream(stream)>>>(plane_sums, db, B, C);
   B200_LAUNCH_OK();
   return 0;
 }
