@@ -119,7 +119,8 @@ int b200ddp_softmax_ce(const float* logits, const long long* labels, float* loss
  * wmat: weight matrix [Cout][ldw] (torch's [Cout][Cin][KH][KW] flattened; ldw % 4 == 0, use weight_prep mode 0 to
  * pad). ktab: device table of int32 pairs, one per k = (ci,kh,kw), padded to a multiple of 128 pairs:
  * {ci*H*W + kh*W + kw, 1 << kh | 1 << (16 + kw)} and {0, 1 << 31} beyond K (k_order 0; KH, KW <= 15). k_order 1 = reduction index
- * ordered (kh,kw,ci) — needs Cin % 32 == 0, no table, weights permuted by weight_prep mode 2 / 3; dw is always
+ * ordered channel-block-major (ci/32, kh, kw, ci%32) — needs Cin % 32 == 0, no table, weights permuted by weight_prep
+ * mode 2 / 3; dw is always
  * returned in torch's [Cout][Cin][KH][KW] order. TF32 tensor cores (gathered operands rounded), fp32 accumulate.
  * dgrad of a stride-1 convolution = conv2d_fwd on dy with weight_prep mode 1 weights and pad' = KH-1-pad. */
 int b200ddp_conv2d_fwd(const float* x, const float* wmat, long long ldw, const float* bias, float* y, const int* ktab,
@@ -133,7 +134,7 @@ int b200ddp_conv2d_wgrad(const float* x, const float* dy, float* dw, const int* 
                          void* stream);
 /* mode 0: out[co][0..ld_out) = w[co][:] zero padded; mode 1: flipped / transposed weights for dgrad,
  * out[ci][co*KH*KW + (KH-1-kh)*KW + (KW-1-kw)] = w[co][ci][kh][kw], row stride ld_out; modes 2 / 3: the same two
- * matrices with the reduction index in channel-inner order (k_order 1). */
+ * matrices with the reduction index in channel-block-major order (k_order 1). */
 int b200ddp_conv2d_weight_prep(const float* w, float* out, int Cout, int Cin, int KH, int KW, long long ld_out, int mode,
                                int device, void* stream);
 /* Several weight_prep jobs in one launch (at most 16): what a training step needs for all conv layers at once. */

@@ -169,7 +169,7 @@ def _conv_tables(device, Cin: int, H: int, W: int, KH: int, KW: int):
 
 
 def _k_order(cin: int) -> int:
-    """1 = reduction index ordered (kh, kw, ci) (needs Cin % 32 == 0), 0 = torch's (ci, kh, kw) with a table."""
+    """1 = reduction index ordered (ci//32, kh, kw, ci%32) (needs Cin % 32 == 0), 0 = torch's (ci, kh, kw) + table."""
     return 1 if cin % 32 == 0 else 0
 
 
@@ -187,7 +187,7 @@ def conv2d_forward_raw(x, wmat, ldw, bias, Cout, KH, KW, stride, pad, relu, k_or
 
 
 def conv_weight_matrix(w, mode: int):
-    """Weight matrix for the implicit GEMM (b200ddp_conv2d_weight_prep): mode 0 padded copy / 2 channel-inner
+    """Weight matrix for the implicit GEMM (b200ddp_conv2d_weight_prep): mode 0 padded copy / 2 channel-block-major
     forward weights [Cout][K]; 1 / 3 flipped, transposed dgrad weights [Cin][Cout*KH*KW]."""
     L = _lib.load()
     Cout, Cin, KH, KW = w.shape

@@ -21,7 +21,7 @@
 //
 // Two orderings of the reduction index k (the weight matrix is permuted to match by conv_weight_prep):
 //   k_order 0  k = (ci, kh, kw)   torch's own order; per-k offsets come from a small device table. Any Cin.
-//   k_order 1  k = (kh, kw, ci)   "channel inner", needs Cin % 32 == 0: a whole 32-row k-block shares one
+//   k_order 1  k = (ci/32, kh, kw, ci%32)   "channel-block-major", needs Cin % 32 == 0: a whole 32-row k-block shares one
 //              (kh, kw), so each producer thread does ONE bounds test per k-block and walks the channels
 //              with a constant stride of H*W — ~6 instructions per gathered element instead of ~20.
 //
@@ -44,7 +44,7 @@ constexpr int CBK = 32;             // fp32 per k-block (128 bytes)
 constexpr int CUK = 8;              // K per tcgen05.mma kind::tf32
 constexpr int kGroups = 3;          // forward / dgrad: 3 producer groups x 32 loads in flight per thread
 constexpr int kProdWarps = 4 * kGroups;
-constexpr int kConvThreads = 32 * (kProdWarps + 1);   // producer/epilogue warps + 1 warp: TMEM alloc + MMA issue
+constexpr int kConvThreads = 32 * (kProdWarps + 2);   // producer/epilogue warps + MMA warp (+ TMEM alloc) + weight-TMA warp
 constexpr int kWgGroups = 3;        // wgrad: 3 producer groups, batches of 32 loads software-pipelined in registers
 constexpr int kWgProdWarps = 4 * kWgGroups;
 constexpr int kWgThreads = 32 * (kWgProdWarps + 1);
@@ -120,7 +120,7 @@ conv_fwd_kernel(const __grid_constant__ CUtensorMap tmW, ConvFwdParams p) {
 
   if (tid == 0) {
     for (int s = 0; s < stages; ++s) {
-      mbar_init(&full_bar[s], 128);     // the 128 threads of one producer group arrive once per phase (+ TMA bytes)
+      mbar_init(&full_bar[s], 128 + 1); // the 128 threads of one producer group + the TMA warp's arrive.expect_tx
       mbar_init(&empty_bar[s], 1);      // tcgen05.commit
     }
     mbar_init(tmem_full_bar, 1);
@@ -157,11 +157,11 @@ conv_fwd_kernel(const __grid_constant__ CUtensorMap tmW, ConvFwdParams p) {
     // smem ring cursor (stage, phase) advance by additions, the per-element address is one IMAD.WIDE
     // (base + r * channel stride), and in the table path the bounds test is one AND + compare against a per-thread
     // mask of valid window rows / columns.
-    const int cb = CI ? (p.Cin >> 5) : 1;      // channel blocks per (kh, kw)
     int cur_cblk = 0, cur_kh = 0, cur_kw = 0;  // CI: position of this group's next k-block to LOAD
-    if (CI) {
-      const int khkw = group / cb;
-      cur_cblk = group - khkw * cb;
+    if (CI) {       // k-block kb = cblk * KH*KW + kh*KW + kw  (channel-block-major: the 32 channel planes of a
+      const int khw = p.KH * p.KW;       // block are swept by all taps back to back, so they stay in L1)
+      cur_cblk = group / khw;
+      const int khkw = group - cur_cblk * khw;
       cur_kh = khkw / p.KW;
       cur_kw = khkw - cur_kh * p.KW;
     }
@@ -190,11 +190,12 @@ conv_fwd_kernel(const __grid_constant__ CUtensorMap tmW, ConvFwdParams p) {
         const bool ok = valid_m && (unsigned)(ih0 + cur_kh) < (unsigned)p.H && (unsigned)(iw0 + cur_kw) < (unsigned)p.W;
         const char* q = xb + (((long long)(cur_cblk << 5) * hw + cur_kh * p.W + cur_kw) << 2);
         load_strided<PL>(q, hw4, ok ? CBK : 0, v);     // constant stride H*W between channels
-        cur_cblk += kGroups;
-        while (cur_cblk >= cb) {
-          cur_cblk -= cb;
-          if (++cur_kw == p.KW) { cur_kw = 0; ++cur_kh; }
-        }
+#pragma unroll
+        for (int t = 0; t < kGroups; ++t)
+          if (++cur_kw == p.KW) {
+            cur_kw = 0;
+            if (++cur_kh == p.KH) { cur_kh = 0; ++cur_cblk; }
+          }
       } else {
         const int2* tab = p.tab + kb * CBK;
 #pragma unroll
@@ -212,12 +213,7 @@ conv_fwd_kernel(const __grid_constant__ CUtensorMap tmW, ConvFwdParams p) {
       B200_TRACE(kb, 6);
       mbar_wait(&empty_bar[c_stage], c_phase ^ 1u);
       B200_TRACE(kb, 1);
-      uint8_t* sa = smem + (size_t)c_stage * STAGE_BYTES;
-      if (gtid == 0) {
-        mbar_expect_tx(&full_bar[c_stage], B_BYTES);
-        tma_load_2d(sa + A_BYTES, &tmW, &full_bar[c_stage], kb * CBK, n0);       // box {32 k, BN co}
-      }
-      const uint32_t sdst = smem_u32(sa);
+      const uint32_t sdst = smem_u32(smem + (size_t)c_stage * STAGE_BYTES);
       uint32_t sd[4];
 #pragma unroll
       for (int c = 0; c < 4; ++c) sd[c] = sdst + s_chunk[c];
@@ -265,7 +261,7 @@ conv_fwd_kernel(const __grid_constant__ CUtensorMap tmW, ConvFwdParams p) {
         }
       }
     }
-  } else {
+  } else if (warp == kProdWarps) {
     // ---------------- MMA issuer ----------------
     const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | (1u << 15) /* A MN-major */ |
                            ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(CBM >> 4) << 24);
@@ -273,6 +269,17 @@ conv_fwd_kernel(const __grid_constant__ CUtensorMap tmW, ConvFwdParams p) {
                               operand_k_major(), smem_u32(&full_bar[0]), smem_u32(&empty_bar[0]),
                               smem_u32(tmem_full_bar), stages, p.kblocks,
                               (blockIdx.x == 0 && blockIdx.y == 0) ? p.trace : nullptr);
+  } else if (lane == 0) {
+    // ---------------- weight-tile TMA producer: runs the whole ring ahead of the gather groups, so the B tile of
+    // a stage is requested the moment the stage frees up instead of when a gather group gets round to it ----------------
+    int s = 0;
+    uint32_t ph = 0;
+    for (int kb = 0; kb < p.kblocks; ++kb) {
+      mbar_wait(&empty_bar[s], ph ^ 1u);
+      mbar_arrive_expect_tx(&full_bar[s], B_BYTES);
+      tma_load_2d(smem + (size_t)s * STAGE_BYTES + A_BYTES, &tmW, &full_bar[s], kb * CBK, n0);    // box {32 k, BN co}
+      if (++s == stages) { s = 0; ph ^= 1u; }
+    }
   }
   tc_fence_before();
   __syncthreads();
@@ -340,11 +347,14 @@ conv_wgrad_kernel(ConvWgradParams p) {
     uint32_t s_chunk[8];
 #pragma unroll
     for (int c = 0; c < 8; ++c) s_chunk[c] = ((c16 ^ (uint32_t)c) << 4) + e16;
-    // channel-inner order: the warp's 32 rows k0..k0+31 share one (kh, kw) and cover channels ci0..ci0+31
+    // channel-block-major order: the warp's 32 rows k0..k0+31 are one (channel block, kh, kw) = 32 channels of a tap;
+    // the four warps of a tile read (mostly) the same 32 channel planes at neighbouring taps -> L1 hits
     const int k0 = m0 + gwarp * 32;
     const bool rows_valid = k0 < p.K;
-    const int khkw_w = CI ? (rows_valid ? k0 / p.Cin : 0) : 0;
-    const int ci0_w = CI ? (rows_valid ? k0 - khkw_w * p.Cin : 0) : 0;
+    const int khw_n = p.KH * p.KW;
+    const int slab_w = CI ? (rows_valid ? (k0 >> 5) : 0) : 0;          // = cblk * KH*KW + kh*KW + kw
+    const int cblk_w = slab_w / khw_n, khkw_w = slab_w - cblk_w * khw_n;
+    const int ci0_w = cblk_w << 5;
     const int kh_w = khkw_w / p.KW, kw_w = khkw_w - kh_w * p.KW;
     const long long a_off = CI ? (((long long)ci0_w * hw + kh_w * p.W + kw_w) << 2) : 0;   // bytes, constant per warp
     // Work of one k-block for a thread = batches of <= 32 loads: [A rows] [B rows 0..31] [B rows 32..].
@@ -453,10 +463,12 @@ conv_wgrad_kernel(ConvWgradParams p) {
     const int m = m0 + gwarp * 32 + lane;
     float* ob;
     long long ld;
-    if (CI && p.splits == 1) {       // un-permute (kh,kw,ci) -> torch's (ci,kh,kw) while storing
-      const int khkw = m < p.K ? m / p.Cin : 0;
-      const int ci = m - khkw * p.Cin;
-      ob = p.dw_direct + (long long)ci * (p.KH * p.KW) + khkw;
+    if (CI && p.splits == 1) {       // un-permute (cblk,kh,kw,ci%32) -> torch's (ci,kh,kw) while storing
+      const int khw_e = p.KH * p.KW;
+      const int mm = m < p.K ? m : 0;
+      const int slab_e = mm >> 5, cblk_e = slab_e / khw_e, khkw = slab_e - cblk_e * khw_e;
+      const int ci = (cblk_e << 5) + (mm & 31);
+      ob = p.dw_direct + (long long)ci * khw_e + khkw;
       ld = p.K;
     } else {
       ob = p.out + (long long)z * p.Cout * p.K + m;
@@ -485,14 +497,15 @@ conv_wgrad_kernel(ConvWgradParams p) {
   if (warp == kWgProdWarps) tmem_dealloc(tmem_base, tmem_cols<BN>());
 }
 
-// dW[co][ci][kh][kw] = sum_z ws[z][co][(kh*KW + kw)*Cin + ci]   (k_order 1 partials -> torch order)
+// dW[co][ci][kh][kw] = sum_z ws[z][co][((ci/32)*KH*KW + kh*KW + kw)*32 + ci%32]   (k_order 1 partials -> torch order)
 __global__ void __launch_bounds__(256) wgrad_finalize_ci_kernel(const float* __restrict__ ws, int splits, int Cout, int Cin,
                                                                 int KHW, float* __restrict__ dw) {
   const long long K = (long long)Cin * KHW, total = (long long)Cout * K, stride = (long long)gridDim.x * blockDim.x;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
-    // i enumerates the GEMM order (coalesced reads): co, khkw, ci
+    // i enumerates the GEMM order (coalesced reads): co, (cblk, khkw, ci % 32)
     const long long co = i / K, k = i - co * K;
-    const int khkw = (int)(k / Cin), ci = (int)(k - (long long)khkw * Cin);
+    const int slab = (int)(k >> 5), cblk = slab / KHW, khkw = slab - cblk * KHW;
+    const int ci = (cblk << 5) + (int)(k & 31);
     float s = 0.f;
     for (int z = 0; z < splits; ++z) s += __ldg(ws + (long long)z * total + i);
     dw[co * K + (long long)ci * KHW + khkw] = s;
@@ -501,8 +514,8 @@ __global__ void __launch_bounds__(256) wgrad_finalize_ci_kernel(const float* __r
 
 // mode 0: out[co][k] = w[co][k] for k < K, zero padding up to ld_out (row stride multiple of 4 for TMA)
 // mode 1: dgrad weights, k' = (co, kh', kw'):  out[ci][co*KH*KW + (KH-1-kh)*KW + (KW-1-kw)] = w[co][ci][kh][kw]
-// mode 2: forward weights in channel-inner order:  out[co][(kh*KW + kw)*Cin + ci]             = w[co][ci][kh][kw]
-// mode 3: dgrad weights in channel-inner order:    out[ci][((KH-1-kh)*KW + (KW-1-kw))*Cout + co] = w[co][ci][kh][kw]
+// mode 2: forward weights, channel-block-major:  out[co][((ci/32)*KHW + kh*KW + kw)*32 + ci%32]               = w[co][ci][kh][kw]
+// mode 3: dgrad weights, channel-block-major:    out[ci][((co/32)*KHW + (KH-1-kh)*KW + (KW-1-kw))*32 + co%32] = w[co][ci][kh][kw]
 __device__ __forceinline__ void weight_prep_body(const float* __restrict__ w, float* __restrict__ out, int Cout, int Cin,
                                                  int KH, int KW, long long ld_out, int mode, long long first,
                                                  long long stride) {
@@ -524,8 +537,8 @@ __device__ __forceinline__ void weight_prep_body(const float* __restrict__ w, fl
       t /= KH;
       const int ci = (int)(t % Cin), co = (int)(t / Cin);
       const float v = __ldg(w + i);
-      if (mode == 2) out[(long long)co * ld_out + (long long)(kh * KW + kw) * Cin + ci] = v;
-      else out[(long long)ci * ld_out + (long long)((KH - 1 - kh) * KW + (KW - 1 - kw)) * Cout + co] = v;
+      if (mode == 2) out[(long long)co * ld_out + ((long long)(ci >> 5) * KHW + kh * KW + kw) * 32 + (ci & 31)] = v;
+      else out[(long long)ci * ld_out + ((long long)(co >> 5) * KHW + (KH - 1 - kh) * KW + (KW - 1 - kw)) * 32 + (co & 31)] = v;
     }
   } else {
     const long long total = (long long)Cout * Cin * KHW;
@@ -702,7 +715,7 @@ int b200ddp_conv2d_fwd(const float* x, const float* wmat, long long ldw, const f
                        int k_order, int Nb, int Cin, int H, int W, int Cout, int KH, int KW, int stride, int pad, int relu,
                        int device, void* stream) {
   B200_CHECK_ARG(x && wmat && y, "conv2d_fwd: null argument");
-  B200_CHECK_ARG(k_order == 0 || k_order == 1, "conv2d_fwd: k_order must be 0 (ci,kh,kw) or 1 (kh,kw,ci)");
+  B200_CHECK_ARG(k_order == 0 || k_order == 1, "conv2d_fwd: k_order must be 0 (ci,kh,kw) or 1 (ci/32,kh,kw,ci%%32)");
   B200_CHECK_ARG(k_order == 1 || (ktab && ((uintptr_t)ktab & 7) == 0), "conv2d_fwd: k_order 0 needs an 8-byte aligned ktab");
   B200_CHECK_ARG(k_order == 0 || (Cin % 32) == 0, "conv2d_fwd: k_order 1 needs Cin %% 32 == 0 (Cin = %d)", Cin);
   B200_CHECK_ARG(k_order == 1 || (KH <= 15 && KW <= 15), "conv2d_fwd: k_order 0 supports kernel sizes up to 15 (got %dx%d)", KH, KW);
@@ -724,7 +737,9 @@ int b200ddp_conv2d_fwd(const float* x, const float* wmat, long long ldw, const f
 #endif
   const int bn = pick_bn(Cout);
   const size_t stage_bytes = (size_t)(CBM + bn) * CBK * 4;
-  int stages = (int)((200 * 1024) / stage_bytes);
+  // channel-block-major order lives off L1 hits (a 32-channel slab of the tile's rows is re-read by every tap):
+  // keep the ring at <= 160 KB so that ~90 KB of the 256 KB SM array stays L1
+  int stages = (int)(((k_order == 1 ? 160 : 200) * 1024) / stage_bytes);
   if (stages > 8) stages = 8;
   if (stages > p.kblocks) stages = p.kblocks;
   if (stages < kGroups) stages = kGroups;
