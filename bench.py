@@ -487,7 +487,7 @@ def run_b200(args) -> None:
                               "traffic": ncu_traffic(f"adam_step_flat n={n_arena}"), "algorithmic_bytes_per_launch": adam_bytes,
                               "avg_launch_ms": adam_t * 1e3, "peak_source": peak_src,
                               "share_of_step": adam_t * 1e3 / (ms_max / args.steps)},
-            "kernels": kernels[:12],
+            "kernels": kernels[:24],
             "final_loss": final_loss,
             "nccl": None,
         }

@@ -117,7 +117,7 @@ int b200ddp_softmax_ce(const float* logits, const long long* labels, float* loss
 /* Replace nn.Conv2d forward / backward (cuDNN TF32 implicit GEMM + NCHW<->NHWC conversions) of torchvision
  * alexnet.py:22,25,28,30,32, reached from reference :121 / :125. x [Nb][Cin][H][W], y [Nb][Cout][OH][OW], fp32 NCHW.
  * wmat: weight matrix [Cout][ldw] (torch's [Cout][Cin][KH][KW] flattened; ldw % 4 == 0, use weight_prep mode 0 to
- * pad). ktab: device table of int32 pairs, one per k = (ci,kh,kw), padded to a multiple of 128 pairs:
+ * pad). ktab: device table of int32 pairs, one per k = (ci,kh,kw), padded to a multiple of 384 pairs:
  * {ci*H*W + kh*W + kw, 1 << kh | 1 << (16 + kw)} and {0, 1 << 31} beyond K (k_order 0; KH, KW <= 15). k_order 1 = reduction index
  * ordered channel-block-major (ci/32, kh, kw, ci%32) — needs Cin % 32 == 0, no table, weights permuted by weight_prep
  * mode 2 / 3; dw is always

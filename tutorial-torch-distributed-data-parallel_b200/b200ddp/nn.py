@@ -148,12 +148,12 @@ _CONV_TABLES: dict = {}
 def _conv_tables(device, Cin: int, H: int, W: int, KH: int, KW: int):
     """int32 device table of pairs indexed by k = (ci, kh, kw): {input offset, window-position bits
     1 << kh | 1 << (16 + kw)} (the kernels AND them with a per-pixel mask of in-image rows / columns).
-    Padded to a multiple of 128 pairs with {0, 1 << 31} = never valid (host logic; built once per shape)."""
+    Padded to a multiple of 384 pairs with {0, 1 << 31} = never valid (host logic; built once per shape)."""
     key = (str(device), Cin, H, W, KH, KW)
     t = _CONV_TABLES.get(key)
     if t is None:
         K = Cin * KH * KW
-        kp = (K + 127) // 128 * 128
+        kp = (K + 383) // 384 * 384            # covers 128-row and 3 x 128-row tile grids
         k = torch.arange(kp, dtype=torch.int64)
         ci, rem = k // (KH * KW), k % (KH * KW)
         kh, kw = rem // KW, rem % KW

@@ -296,15 +296,23 @@ struct ConvWgradParams {
   int K, M, OHW, kblocks_total, kblocks_per_split, splits, stages;
 };
 
-template <int BN, int PL>       // PL as in conv_fwd_kernel; PL > 0 additionally means OH*OW == H*W == PL
+constexpr uint32_t tmem_cols_for(int n) { return n <= 32 ? 32 : n <= 64 ? 64 : n <= 128 ? 128 : n <= 256 ? 256 : 512; }
+
+// PL as in conv_fwd_kernel; PL > 0 additionally means OH*OW == H*W == PL.
+// R = 128-row sub-tiles of the gradient matrix per CTA (R*BN <= 512 TMEM columns). The kernel is bound by the bytes
+// it gathers (12 warps x 32 loads in flight against ~1900 cycles of L2 latency under load): a CTA that owns R*128
+// k-rows gathers the dY tile once for R accumulators instead of once per accumulator (-30 % gathered bytes at R = 2).
+template <int BN, int PL, int R>
 __global__ void __launch_bounds__(kWgThreads, 1)
 conv_wgrad_kernel(ConvWgradParams p) {
   constexpr bool CI = PL >= 0;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  constexpr uint32_t A_BYTES = CBM * CBK * 4;
+  constexpr uint32_t A_SUB_BYTES = CBM * CBK * 4;
+  constexpr uint32_t A_BYTES = R * A_SUB_BYTES;
   constexpr uint32_t B_BYTES = BN * CBK * 4;
   constexpr uint32_t STAGE_BYTES = A_BYTES + B_BYTES;
+  constexpr uint32_t TMEM_COLS = tmem_cols_for(R * BN);
   const int stages = p.stages;
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + (size_t)stages * STAGE_BYTES);
   uint64_t* empty_bar = full_bar + stages;
@@ -313,13 +321,14 @@ conv_wgrad_kernel(ConvWgradParams p) {
   int2* s_tab = reinterpret_cast<int2*>(tmem_slot + 4);
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int m0 = blockIdx.x * CBM, n0 = blockIdx.y * BN, z = blockIdx.z;
+  const int m0 = blockIdx.x * (CBM * R), n0 = blockIdx.y * BN, z = blockIdx.z;
   const int kb_begin = z * p.kblocks_per_split;
   int kb_end = kb_begin + p.kblocks_per_split;
   if (kb_end > p.kblocks_total) kb_end = p.kblocks_total;
   const int nkb = kb_end - kb_begin;
 
-  if (!CI && tid < CBM) s_tab[tid] = __ldg(p.tab + m0 + tid);
+  if (!CI)
+    for (int t = tid; t < CBM * R; t += blockDim.x) s_tab[t] = __ldg(p.tab + m0 + t);   // table is padded to the tile grid
   if (tid == 0) {
     for (int s = 0; s < stages; ++s) {
       mbar_init(&full_bar[s], 128);
@@ -328,14 +337,14 @@ conv_wgrad_kernel(ConvWgradParams p) {
     mbar_init(tmem_full_bar, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
-  if (warp == kWgProdWarps) tmem_alloc(tmem_slot, tmem_cols<BN>());
+  if (warp == kWgProdWarps) tmem_alloc(tmem_slot, TMEM_COLS);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp < kWgProdWarps) {
-    // ---------------- producers: lane <-> pixel of the k-block, warp <-> quarter of the tile rows,
+    // ---------------- producers: lane <-> pixel of the k-block, warp <-> quarter of each sub-tile's rows,
     //                  group <-> every kWgGroups-th k-block ----------------
     const int group = warp >> 2, gwarp = warp & 3;
     constexpr int B_ROWS = BN / 4;
@@ -347,25 +356,22 @@ conv_wgrad_kernel(ConvWgradParams p) {
     uint32_t s_chunk[8];
 #pragma unroll
     for (int c = 0; c < 8; ++c) s_chunk[c] = ((c16 ^ (uint32_t)c) << 4) + e16;
-    // channel-block-major order: the warp's 32 rows k0..k0+31 are one (channel block, kh, kw) = 32 channels of a tap;
-    // the four warps of a tile read (mostly) the same 32 channel planes at neighbouring taps -> L1 hits
-    const int k0 = m0 + gwarp * 32;
-    const bool rows_valid = k0 < p.K;
+    // channel-block-major order: a warp's 32 rows of a sub-tile are one (channel block, kh, kw) = 32 channels of a
+    // tap; the warps of a tile read (mostly) the same 32 channel planes at neighbouring taps -> L1 hits
     const int khw_n = p.KH * p.KW;
-    const int slab_w = CI ? (rows_valid ? (k0 >> 5) : 0) : 0;          // = cblk * KH*KW + kh*KW + kw
-    const int cblk_w = slab_w / khw_n, khkw_w = slab_w - cblk_w * khw_n;
-    const int ci0_w = cblk_w << 5;
-    const int kh_w = khkw_w / p.KW, kw_w = khkw_w - kh_w * p.KW;
-    const long long a_off = CI ? (((long long)ci0_w * hw + kh_w * p.W + kw_w) << 2) : 0;   // bytes, constant per warp
-    // Work of one k-block for a thread = batches of <= 32 loads: [A rows] [B rows 0..31] [B rows 32..].
-    // Software pipeline in registers: the loads of the NEXT batch are issued before the current batch is stored
-    // (and before the current k-block's smem slot is known to be free), so a batch of loads is always in flight.
-    // Instruction economy as in the forward kernel: cursors advance by additions, pixel -> (image, row, column)
-    // uses float reciprocals (exact: pixel index < 2^23, quotient error << 1/(2*OHW)), one IMAD.WIDE per address.
-    constexpr int NB = 1 + (B_ROWS + 31) / 32;
+    const float inv_khw = 1.0f / (float)khw_n, inv_kw = 1.0f / (float)p.KW;
+    // Work of one k-block for a thread = batches of <= 32 loads: [A rows of sub-tile 0] .. [A rows of sub-tile R-1]
+    // [B rows 0..31] [B rows 32..]. Software pipeline in registers: the loads of the NEXT batch are issued before the
+    // current batch is stored (and before the current k-block's smem slot is known to be free), so a batch of loads
+    // is always in flight. Cursors advance by additions, index splits use float reciprocals (exact: operands < 2^23,
+    // quotient error << half a step), addresses are `base + immediate` (PL > 0) or a walking 64-bit pointer.
+    constexpr int NB = R + (B_ROWS + 31) / 32;
     int li = group, lt = 0;            // load cursor: (k-block, batch)
     int l_pxl = kb_begin * CBK + group * CBK + lane;   // pixel of this lane in k-block li
     bool l_valid = false;
+    int l_ih0 = 0, l_iw0 = 0;
+    uint32_t l_mask = 0;
+    const char* l_xb = reinterpret_cast<const char*>(p.x);
     const char* l_dyb = reinterpret_cast<const char*>(p.dy);
     auto load = [&](float (&v)[32]) {
       if (lt == 0) {
@@ -375,16 +381,13 @@ conv_wgrad_kernel(ConvWgradParams p) {
         if (pix < 0) { --n_img; pix += p.OHW; } else if (pix >= p.OHW) { ++n_img; pix -= p.OHW; }   // never taken at these sizes
         int oh = (int)(((float)pix + 0.5f) * inv_ow), ow = pix - oh * p.OW;
         if (ow < 0) { --oh; ow += p.OW; } else if (ow >= p.OW) { ++oh; ow -= p.OW; }
-        const int ih0 = oh * p.stride - p.pad, iw0 = ow * p.stride - p.pad;
-        const char* xb = reinterpret_cast<const char*>(p.x + ((long long)n_img * p.Cin * hw + (long long)ih0 * p.W + iw0));
+        l_ih0 = oh * p.stride - p.pad;
+        l_iw0 = ow * p.stride - p.pad;
+        l_xb = reinterpret_cast<const char*>(p.x + ((long long)n_img * p.Cin * hw + (long long)l_ih0 * p.W + l_iw0));
         l_dyb = reinterpret_cast<const char*>(p.dy + ((long long)n_img * p.Cout * p.OHW + pix));
         l_pxl += kWgGroups * CBK;
-        if (CI) {
-          const bool ok = l_valid && rows_valid && (unsigned)(ih0 + kh_w) < (unsigned)p.H && (unsigned)(iw0 + kw_w) < (unsigned)p.W;
-          const char* q = xb + a_off;
-          load_strided<PL>(q, hw4, ok ? 32 : 0, v);
-        } else {
-          uint32_t win_mask = 0;
+        if (!CI) {
+          l_mask = 0;
           if (l_valid) {
             auto span = [](int i0, int n, int limit) -> uint32_t {
               const int lo = i0 < 0 ? -i0 : 0;
@@ -392,18 +395,34 @@ conv_wgrad_kernel(ConvWgradParams p) {
               hi = hi > n ? n : hi;
               return hi > lo ? (((1u << hi) - 1u) & ~((1u << lo) - 1u)) : 0u;
             };
-            win_mask = span(ih0, p.KH, p.H) | (span(iw0, p.KW, p.W) << 16);
+            l_mask = span(l_ih0, p.KH, p.H) | (span(l_iw0, p.KW, p.W) << 16);
           }
+        }
+      }
+      if (lt < R) {
+        const int k0 = m0 + lt * CBM + gwarp * 32;         // first of this warp's 32 rows in sub-tile lt
+        if (CI) {
+          const bool rows_valid = k0 < p.K;
+          const int slab = rows_valid ? (k0 >> 5) : 0;     // = cblk * KH*KW + kh*KW + kw
+          int cblk = (int)(((float)slab + 0.5f) * inv_khw), khkw = slab - cblk * khw_n;
+          if (khkw < 0) { --cblk; khkw += khw_n; } else if (khkw >= khw_n) { ++cblk; khkw -= khw_n; }
+          int kh = (int)(((float)khkw + 0.5f) * inv_kw), kw = khkw - kh * p.KW;
+          if (kw < 0) { --kh; kw += p.KW; } else if (kw >= p.KW) { ++kh; kw -= p.KW; }
+          const bool ok = l_valid && rows_valid && (unsigned)(l_ih0 + kh) < (unsigned)p.H && (unsigned)(l_iw0 + kw) < (unsigned)p.W;
+          const char* q = l_xb + (((long long)(cblk << 5) * hw + kh * p.W + kw) << 2);
+          load_strided<PL>(q, hw4, ok ? 32 : 0, v);
+        } else {
+          const int2* tb = s_tab + lt * CBM + gwarp * 32;
 #pragma unroll
           for (int j = 0; j < 32; ++j) {
-            const int2 t = s_tab[gwarp * 32 + j];
+            const int2 t = tb[j];
             v[j] = 0.f;
-            if ((win_mask & (uint32_t)t.y) == (uint32_t)t.y)
-              v[j] = __ldg(reinterpret_cast<const float*>(xb + ((unsigned long long)(uint32_t)t.x << 2)));
+            if ((l_mask & (uint32_t)t.y) == (uint32_t)t.y)
+              v[j] = __ldg(reinterpret_cast<const float*>(l_xb + ((unsigned long long)(uint32_t)t.x << 2)));
           }
         }
       } else {
-        const int r0 = (lt - 1) * 32;
+        const int r0 = (lt - R) * 32;
         const int co0 = n0 + gwarp * B_ROWS + r0;
         int nrows = B_ROWS - r0;                       // rows of this batch that exist in the tile and the tensor
         if (nrows > p.Cout - co0) nrows = p.Cout - co0;
@@ -418,16 +437,16 @@ conv_wgrad_kernel(ConvWgradParams p) {
     uint32_t c_phase = 0;
     auto store = [&](const float (&v)[32]) {
       const uint32_t sa = smem_u32(smem + (size_t)c_stage * STAGE_BYTES);
-      if (st_ == 0) {
-        mbar_wait(&empty_bar[c_stage], c_phase ^ 1u);
+      if (st_ == 0) mbar_wait(&empty_bar[c_stage], c_phase ^ 1u);
+      if (st_ < R) {
         uint32_t sd[8];
 #pragma unroll
-        for (int c = 0; c < 8; ++c) sd[c] = sa + (uint32_t)(gwarp * 32) * 128u + s_chunk[c];
+        for (int c = 0; c < 8; ++c) sd[c] = sa + (uint32_t)st_ * A_SUB_BYTES + (uint32_t)(gwarp * 32) * 128u + s_chunk[c];
 #pragma unroll
         for (int j = 0; j < 32; ++j)      // (gwarp*32 + j) & 7 == j & 7
           sts_f32(sd[j & 7] + (uint32_t)j * 128u, round_tf32(v[j]));
       } else {
-        const int r0 = (st_ - 1) * 32;
+        const int r0 = (st_ - R) * 32;
         const int nrows = B_ROWS - r0;
         uint32_t sd[8];
 #pragma unroll
@@ -457,44 +476,44 @@ conv_wgrad_kernel(ConvWgradParams p) {
         store(rb);
       }
     }
-    // ---------------- epilogue: TMEM lane = k index, columns = output channels ----------------
+    // ---------------- epilogue: TMEM lane = k index, columns [sub*BN, sub*BN + BN) = output channels of sub-tile `sub` ----------------
     mbar_wait(tmem_full_bar, 0);
     tc_fence_after();
-    const int m = m0 + gwarp * 32 + lane;
-    float* ob;
-    long long ld;
-    if (CI && p.splits == 1) {       // un-permute (cblk,kh,kw,ci%32) -> torch's (ci,kh,kw) while storing
-      const int khw_e = p.KH * p.KW;
-      const int mm = m < p.K ? m : 0;
-      const int slab_e = mm >> 5, cblk_e = slab_e / khw_e, khkw = slab_e - cblk_e * khw_e;
-      const int ci = (cblk_e << 5) + (mm & 31);
-      ob = p.dw_direct + (long long)ci * khw_e + khkw;
-      ld = p.K;
-    } else {
-      ob = p.out + (long long)z * p.Cout * p.K + m;
-      ld = p.K;
-    }
 #pragma unroll 1
-    for (int c = group * 32; c < BN; c += 32 * kWgGroups) {
-      uint32_t r[32];
-      tmem_ld_32x32(tmem_base + ((uint32_t)(gwarp * 32) << 16) + (uint32_t)c, r);
-      if (m < p.K) {
+    for (int sub = 0; sub < R; ++sub) {
+      const int m = m0 + sub * CBM + gwarp * 32 + lane;
+      float* ob;
+      const long long ld = p.K;
+      if (CI && p.splits == 1) {       // un-permute (cblk,kh,kw,ci%32) -> torch's (ci,kh,kw) while storing
+        const int mm = m < p.K ? m : 0;
+        const int slab_e = mm >> 5, cblk_e = slab_e / khw_n, khkw = slab_e - cblk_e * khw_n;
+        const int ci = (cblk_e << 5) + (mm & 31);
+        ob = p.dw_direct + (long long)ci * khw_n + khkw;
+      } else {
+        ob = p.out + (long long)z * p.Cout * p.K + m;
+      }
+#pragma unroll 1
+      for (int c = group * 32; c < BN; c += 32 * kWgGroups) {
+        uint32_t r[32];
+        tmem_ld_32x32(tmem_base + ((uint32_t)(gwarp * 32) << 16) + (uint32_t)(sub * BN + c), r);
+        if (m < p.K) {
 #pragma unroll
-        for (int j = 0; j < 32; ++j) {
-          const int co = n0 + c + j;
-          if (co < p.Cout) ob[(long long)co * ld] = __uint_as_float(r[j]);
+          for (int j = 0; j < 32; ++j) {
+            const int co = n0 + c + j;
+            if (co < p.Cout) ob[(long long)co * ld] = __uint_as_float(r[j]);
+          }
         }
       }
     }
   } else {
     const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(CBM >> 4) << 24);
-    mma_issue_loop<CBK / CUK>(tmem_base, idesc, smem_u32(smem), STAGE_BYTES, A_BYTES, operand_k_major(),
-                              operand_k_major(), smem_u32(&full_bar[0]), smem_u32(&empty_bar[0]),
-                              smem_u32(tmem_full_bar), stages, nkb);
+    mma_issue_loop<CBK / CUK, R>(tmem_base, idesc, smem_u32(smem), STAGE_BYTES, A_BYTES, operand_k_major(),
+                                 operand_k_major(), smem_u32(&full_bar[0]), smem_u32(&empty_bar[0]),
+                                 smem_u32(tmem_full_bar), stages, nkb, nullptr, A_SUB_BYTES, BN);
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == kWgProdWarps) tmem_dealloc(tmem_base, tmem_cols<BN>());
+  if (warp == kWgProdWarps) tmem_dealloc(tmem_base, TMEM_COLS);
 }
 
 // dW[co][ci][kh][kw] = sum_z ws[z][co][((ci/32)*KH*KW + kh*KW + kw)*32 + ci%32]   (k_order 1 partials -> torch order)
@@ -642,24 +661,24 @@ int launch_fwd(const CUtensorMap& tmW, const ConvFwdParams& p, cudaStream_t stre
   return 0;
 }
 
-template <int BN, int PL>
+template <int BN, int PL, int R>
 int launch_wgrad(const ConvWgradParams& p, cudaStream_t stream) {
-  const size_t stage_bytes = (size_t)(CBM + BN) * CBK * 4;
-  const size_t smem = 1024 + (size_t)p.stages * stage_bytes + (2 * p.stages + 1) * 8 + 32 + CBM * 8;
+  const size_t stage_bytes = (size_t)(CBM * R + BN) * CBK * 4;
+  const size_t smem = 1024 + (size_t)p.stages * stage_bytes + (2 * p.stages + 1) * 8 + 32 + (size_t)CBM * R * 8;
   static bool attr_set = false;
   if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(conv_wgrad_kernel<BN, PL>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    cudaError_t e = cudaFuncSetAttribute(conv_wgrad_kernel<BN, PL, R>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
     if (e != cudaSuccess) {
-      set_error("cudaFuncSetAttribute(conv_wgrad_kernel<%d>) -> %s", BN, cudaGetErrorString(e));
+      set_error("cudaFuncSetAttribute(conv_wgrad_kernel<%d,%d,%d>) -> %s", BN, PL, R, cudaGetErrorString(e));
       return kCudaErrBase + (int)e;
     }
     attr_set = true;
   }
-  dim3 grid((p.K + CBM - 1) / CBM, (p.Cout + BN - 1) / BN, p.splits);
-  conv_wgrad_kernel<BN, PL><<<grid, kWgThreads, smem, stream>>>(p);
+  dim3 grid((p.K + CBM * R - 1) / (CBM * R), (p.Cout + BN - 1) / BN, p.splits);
+  conv_wgrad_kernel<BN, PL, R><<<grid, kWgThreads, smem, stream>>>(p);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) {
-    set_error("conv_wgrad_kernel<%d> launch (grid %d,%d,%d smem %zu) -> %s", BN, grid.x, grid.y, grid.z, smem,
+    set_error("conv_wgrad_kernel<%d,%d,%d> launch (grid %d,%d,%d smem %zu) -> %s", BN, PL, R, grid.x, grid.y, grid.z, smem,
               cudaGetErrorString(e));
     return kCudaErrBase + (int)e;
   }
@@ -678,20 +697,26 @@ inline int pick_bn(int Cout) {
 }
 
 struct WgradPlan {
-  int bn, m_tiles, n_tiles, kblocks_total, splits, per;
+  int bn, r, m_tiles, n_tiles, kblocks_total, splits, per;
 };
 
 inline WgradPlan plan_wgrad(int Nb, int Cin, int OH, int OW, int Cout, int KH, int KW) {
   WgradPlan w;
   const int K = Cin * KH * KW;
   w.bn = pick_bn(Cout);
-  w.m_tiles = (K + CBM - 1) / CBM;
+  // row sub-tiles per CTA: 2 for the channel-block-major layers (2*BN <= 512 TMEM columns, 3 stages <= 192 KB),
+  // 3 for the table path with a 64-channel tile (conv1: K = 363 = one CTA row), else 1
+  const bool ci = (Cin % 32) == 0;
+  w.r = 1;
+  if (ci && K > CBM) w.r = 2;
+  if (!ci && w.bn == 64 && K > 2 * CBM) w.r = 3;
+  w.m_tiles = (K + CBM * w.r - 1) / (CBM * w.r);
   w.n_tiles = (Cout + w.bn - 1) / w.bn;
   const long long M = (long long)Nb * OH * OW;
   w.kblocks_total = (int)((M + CBK - 1) / CBK);
   int splits = kNumSMs / (w.m_tiles * w.n_tiles);
   if (splits < 1) splits = 1;
-  if (splits > 64) splits = 64;
+  if (splits > kNumSMs) splits = kNumSMs;
   if (splits > w.kblocks_total) splits = w.kblocks_total;
   w.per = (w.kblocks_total + splits - 1) / splits;
   w.splits = (w.kblocks_total + w.per - 1) / w.per;
@@ -795,7 +820,7 @@ int b200ddp_conv2d_wgrad(const float* x, const float* dy, float* dw, const int* 
   p.stride = stride; p.pad = pad;
   p.K = K; p.M = Nb * OH * OW; p.OHW = OH * OW;
   p.kblocks_total = w.kblocks_total; p.kblocks_per_split = w.per; p.splits = w.splits;
-  const size_t stage_bytes = (size_t)(CBM + w.bn) * CBK * 4;
+  const size_t stage_bytes = (size_t)(CBM * w.r + w.bn) * CBK * 4;
   int stages = (int)((200 * 1024) / stage_bytes);
   if (stages > 6) stages = 6;
   if (stages > w.per) stages = w.per;
@@ -803,20 +828,26 @@ int b200ddp_conv2d_wgrad(const float* x, const float* dy, float* dw, const int* 
   p.stages = stages;
   cudaStream_t s = as_stream(stream);
   int rc;
-#define B200_WG_BN(PLV)                                          \
+#define B200_WG_BN(PLV, RV)                                      \
   switch (w.bn) {                                                \
-    case 64: rc = launch_wgrad<64, PLV>(p, s); break;            \
-    case 128: rc = launch_wgrad<128, PLV>(p, s); break;          \
-    case 192: rc = launch_wgrad<192, PLV>(p, s); break;          \
-    default: rc = launch_wgrad<256, PLV>(p, s); break;           \
+    case 64: rc = launch_wgrad<64, PLV, RV>(p, s); break;        \
+    case 128: rc = launch_wgrad<128, PLV, RV>(p, s); break;      \
+    case 192: rc = launch_wgrad<192, PLV, RV>(p, s); break;      \
+    default: rc = launch_wgrad<256, PLV, RV>(p, s); break;       \
   }
   if (k_order == 1) {
     const int plane = (H * W == OH * OW) ? H * W : 0;            // the compile-time stride serves x and dy
-    if (plane == 27 * 27) { B200_WG_BN(27 * 27) }
-    else if (plane == 13 * 13) { B200_WG_BN(13 * 13) }
-    else { B200_WG_BN(0) }
+    if (w.r == 2) {
+      if (plane == 27 * 27) { B200_WG_BN(27 * 27, 2) }
+      else if (plane == 13 * 13) { B200_WG_BN(13 * 13, 2) }
+      else { B200_WG_BN(0, 2) }
+    } else {
+      B200_WG_BN(0, 1)
+    }
+  } else if (w.r == 3) {
+    rc = launch_wgrad<64, -1, 3>(p, s);
   } else {
-    B200_WG_BN(-1)
+    B200_WG_BN(-1, 1)
   }
 #undef B200_WG_BN
   if (rc) return rc;

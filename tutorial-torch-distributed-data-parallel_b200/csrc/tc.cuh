@@ -183,11 +183,14 @@ __device__ __forceinline__ bool elect_one() {
   return pred != 0;
 }
 
-template <int UMMAS>
+// RSUB > 1: the stage holds RSUB A sub-tiles (a_sub_bytes apart) that share the B tile; sub-tile r accumulates into
+// TMEM columns [r * d_sub_cols, ...).
+template <int UMMAS, int RSUB = 1>
 __device__ __forceinline__ void mma_issue_loop(uint32_t tmem_d, uint32_t idesc, uint32_t smem_saddr, uint32_t stage_bytes,
                                                uint32_t a_bytes, OperandDesc a, OperandDesc b, uint32_t full_saddr,
                                                uint32_t empty_saddr, uint32_t tmem_full_saddr, int stages, int nkb,
-                                               long long* trace = nullptr) {
+                                               long long* trace = nullptr, uint32_t a_sub_bytes = 0,
+                                               uint32_t d_sub_cols = 0) {
   const uint32_t a_lo0 = ((smem_saddr & 0x3FFFFu) >> 4) | ((a.lbo >> 4) << 16);
   const uint32_t b_lo0 = (((smem_saddr + a_bytes) & 0x3FFFFu) >> 4) | ((b.lbo >> 4) << 16);
   const uint32_t a_hi = (a.sbo >> 4) | (1u << 14) | (a.layout_type << 29);
@@ -207,7 +210,11 @@ __device__ __forceinline__ void mma_issue_loop(uint32_t tmem_d, uint32_t idesc, 
     tc_fence_after();
     if (elect_one()) {
 #pragma unroll
-      for (int k = 0; k < UMMAS; ++k) umma_tf32_lohi(tmem_d, a_lo + k * a_step, a_hi, b_lo + k * b_step, b_hi, idesc, k ? 1u : acc);
+      for (int r = 0; r < RSUB; ++r)
+#pragma unroll
+        for (int k = 0; k < UMMAS; ++k)
+          umma_tf32_lohi(tmem_d + r * d_sub_cols, a_lo + r * (a_sub_bytes >> 4) + k * a_step, a_hi, b_lo + k * b_step, b_hi,
+                         idesc, k ? 1u : acc);
       umma_commit_addr(eb);               // frees this smem stage when the MMAs above retire
     }
     acc = 1u;
