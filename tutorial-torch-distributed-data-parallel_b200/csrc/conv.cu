@@ -106,10 +106,14 @@ conv_fwd_kernel(const __grid_constant__ CUtensorMap tmW, ConvFwdParams p) {
   constexpr bool CI = PL >= 0;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  constexpr uint32_t A_BYTES = CBM * CBK * 4;
+  // The im2col tile (A) goes registers -> TENSOR MEMORY (tcgen05.st), not shared memory: ncu showed the unified
+  // L1/shared-memory data pipe as the limiter (gather LDGs + 128 STS + TMA writes + the MMA's own reads of A and B
+  // per k-block); with A in TMEM the STS and the MMA's A reads leave that pipe. Shared memory holds only the
+  // TMA-fed weight tiles. TMEM: accumulator in columns [0, BN), A stage s in [kATmemCol0 + 32 s, +32).
   constexpr uint32_t B_BYTES = BN * CBK * 4;
-  constexpr uint32_t STAGE_BYTES = A_BYTES + B_BYTES;
-  const int stages = p.stages;
+  constexpr uint32_t STAGE_BYTES = B_BYTES;
+  constexpr uint32_t kATmemCol0 = 256, kTmemCols = 512;
+  const int stages = p.stages;                        // <= 8 (8 x 32 A columns)
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + (size_t)stages * STAGE_BYTES);
   uint64_t* empty_bar = full_bar + stages;
   uint64_t* tmem_full_bar = empty_bar + stages;
@@ -127,7 +131,7 @@ conv_fwd_kernel(const __grid_constant__ CUtensorMap tmW, ConvFwdParams p) {
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tmW) : "memory");
   }
-  if (warp == kProdWarps) tmem_alloc(tmem_slot, tmem_cols<BN>());
+  if (warp == kProdWarps) tmem_alloc(tmem_slot, kTmemCols);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -145,13 +149,8 @@ conv_fwd_kernel(const __grid_constant__ CUtensorMap tmW, ConvFwdParams p) {
     const long long hw = (long long)p.H * p.W;
     const uint32_t hw4 = (uint32_t)hw * 4u;                 // byte stride between channels
     const char* xb = reinterpret_cast<const char*>(p.x + ((long long)n_img * p.Cin * hw + (long long)ih0 * p.W + iw0));
-    // MN-major SWIZZLE_128B_BASE32B: k-row r at r*128 B, 32-byte chunk c stored at chunk c ^ (r & 3);
-    // the 32-pixel atom `gwarp` starts at gwarp*4096 B.
-    const uint32_t chunk = (uint32_t)lane >> 3;
-    const uint32_t s_thread = (uint32_t)gwarp * 4096u + ((uint32_t)lane & 7u) * 4u;
-    uint32_t s_chunk[4];
-#pragma unroll
-    for (int c = 0; c < 4; ++c) s_chunk[c] = s_thread + ((chunk ^ (uint32_t)c) << 5);
+    // TMEM address of this warp's lane quarter (a warp may only touch lanes 32*(warp%4) .. +31): lane = tile row
+    const uint32_t t_lane = tmem_base + ((uint32_t)(gwarp * 32) << 16);
     // The producer loops are bound by instruction issue (ncu: 13 instructions per gathered element before this
     // was restructured), so everything that can be hoisted is: the reduction cursor (kh, kw, channel block) and the
     // smem ring cursor (stage, phase) advance by additions, the per-element address is one IMAD.WIDE
@@ -213,14 +212,13 @@ conv_fwd_kernel(const __grid_constant__ CUtensorMap tmW, ConvFwdParams p) {
       B200_TRACE(kb, 6);
       mbar_wait(&empty_bar[c_stage], c_phase ^ 1u);
       B200_TRACE(kb, 1);
-      const uint32_t sdst = smem_u32(smem + (size_t)c_stage * STAGE_BYTES);
-      uint32_t sd[4];
+      uint32_t rr[CBK];
 #pragma unroll
-      for (int c = 0; c < 4; ++c) sd[c] = sdst + s_chunk[c];
-#pragma unroll
-      for (int r = 0; r < CBK; ++r) sts_f32(sd[r & 3] + (uint32_t)r * 128u, round_tf32(v[r]));
+      for (int r = 0; r < CBK; ++r) rr[r] = __float_as_uint(round_tf32(v[r]));
+      tmem_st_32x32(t_lane + kATmemCol0 + (uint32_t)c_stage * CBK, rr);     // row = this thread's pixel, 32 K columns
+      tmem_wait_st();
       B200_TRACE(kb, 7);
-      fence_proxy_async_smem();
+      tc_fence_before();
       mbar_arrive(&full_bar[c_stage]);
       B200_TRACE(kb, 2);
       c_stage += kGroups;
@@ -263,12 +261,10 @@ conv_fwd_kernel(const __grid_constant__ CUtensorMap tmW, ConvFwdParams p) {
     }
   } else if (warp == kProdWarps) {
     // ---------------- MMA issuer ----------------
-    const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | (1u << 15) /* A MN-major */ |
-                           ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(CBM >> 4) << 24);
-    mma_issue_loop<CBK / CUK>(tmem_base, idesc, smem_u32(smem), STAGE_BYTES, A_BYTES, operand_mn_major(),
-                              operand_k_major(), smem_u32(&full_bar[0]), smem_u32(&empty_bar[0]),
-                              smem_u32(tmem_full_bar), stages, p.kblocks,
-                              (blockIdx.x == 0 && blockIdx.y == 0) ? p.trace : nullptr);
+    const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(CBM >> 4) << 24);
+    mma_issue_loop_ts<CBK / CUK>(tmem_base, tmem_base + kATmemCol0, CBK, idesc, smem_u32(smem), STAGE_BYTES,
+                                 operand_k_major(), smem_u32(&full_bar[0]), smem_u32(&empty_bar[0]),
+                                 smem_u32(tmem_full_bar), stages, p.kblocks);
   } else if (lane == 0) {
     // ---------------- weight-tile TMA producer: runs the whole ring ahead of the gather groups, so the B tile of
     // a stage is requested the moment the stage frees up instead of when a gather group gets round to it ----------------
@@ -277,13 +273,13 @@ conv_fwd_kernel(const __grid_constant__ CUtensorMap tmW, ConvFwdParams p) {
     for (int kb = 0; kb < p.kblocks; ++kb) {
       mbar_wait(&empty_bar[s], ph ^ 1u);
       mbar_arrive_expect_tx(&full_bar[s], B_BYTES);
-      tma_load_2d(smem + (size_t)s * STAGE_BYTES + A_BYTES, &tmW, &full_bar[s], kb * CBK, n0);    // box {32 k, BN co}
+      tma_load_2d(smem + (size_t)s * STAGE_BYTES, &tmW, &full_bar[s], kb * CBK, n0);    // box {32 k, BN co}
       if (++s == stages) { s = 0; ph ^= 1u; }
     }
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == kProdWarps) tmem_dealloc(tmem_base, tmem_cols<BN>());
+  if (warp == kProdWarps) tmem_dealloc(tmem_base, kTmemCols);
 }
 
 struct ConvWgradParams {
@@ -639,7 +635,7 @@ inline int cs_splits(int Nb, int C) {
 
 template <int BN, int PL>
 int launch_fwd(const CUtensorMap& tmW, const ConvFwdParams& p, cudaStream_t stream) {
-  const size_t stage_bytes = (size_t)(CBM + BN) * CBK * 4;
+  const size_t stage_bytes = (size_t)BN * CBK * 4;       // weight tile only: the im2col tile lives in TMEM
   const size_t smem = 1024 + (size_t)p.stages * stage_bytes + (2 * p.stages + 1) * 8 + 16;
   static bool attr_set = false;
   if (!attr_set) {
@@ -761,10 +757,9 @@ int b200ddp_conv2d_fwd(const float* x, const float* wmat, long long ldw, const f
   p.trace = g_conv_trace;
 #endif
   const int bn = pick_bn(Cout);
-  const size_t stage_bytes = (size_t)(CBM + bn) * CBK * 4;
-  // channel-block-major order lives off L1 hits (a 32-channel slab of the tile's rows is re-read by every tap):
-  // keep the ring at <= 160 KB so that ~90 KB of the 256 KB SM array stays L1
-  int stages = (int)(((k_order == 1 ? 160 : 200) * 1024) / stage_bytes);
+  // ring depth: 8 A stages fit the TMEM columns left of the accumulator; the weight-tile ring is <= 8 x 32 KB,
+  // which leaves >= ~90 KB of the SM array as L1 for the channel-block-major reuse
+  int stages = (int)((160 * 1024) / ((size_t)bn * CBK * 4));
   if (stages > 8) stages = 8;
   if (stages > p.kblocks) stages = p.kblocks;
   if (stages < kGroups) stages = kGroups;

@@ -231,5 +231,65 @@ __device__ __forceinline__ void mma_issue_loop(uint32_t tmem_d, uint32_t idesc, 
   __syncwarp();
 }
 
+// ---- A operand in tensor memory ("TS" form): tcgen05.mma [d], [a_tmem], b_desc --------------------------------
+// Lane = row of the 128-row tile, one 32-bit column per tf32 K element: a thread that owns one tile row and holds
+// 32 K-values in registers writes them with ONE tcgen05.st (32x32b.x32) - no shared-memory store, no swizzle, and
+// the MMA does not read A through the shared-memory port at all.
+__device__ __forceinline__ void tmem_st_32x32(uint32_t taddr, const uint32_t (&r)[32]) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
+      "{%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,"
+      "%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31,%32};"
+      ::"r"(taddr), "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]),
+        "r"(r[9]), "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15]), "r"(r[16]), "r"(r[17]),
+        "r"(r[18]), "r"(r[19]), "r"(r[20]), "r"(r[21]), "r"(r[22]), "r"(r[23]), "r"(r[24]), "r"(r[25]), "r"(r[26]),
+        "r"(r[27]), "r"(r[28]), "r"(r[29]), "r"(r[30]), "r"(r[31])
+      : "memory");
+}
+__device__ __forceinline__ void tmem_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+
+__device__ __forceinline__ void umma_tf32_ts(uint32_t tmem_d, uint32_t tmem_a, uint32_t b_lo, uint32_t b_hi, uint32_t idesc,
+                                             uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t.reg .b64 db;\n\t"
+      "setp.ne.b32 p, %5, 0;\n\t"
+      "mov.b64 db, {%2, %3};\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], db, %4, p;\n\t}"
+      ::"r"(tmem_d), "r"(tmem_a), "r"(b_lo), "r"(b_hi), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+
+// MMA loop for the TS form: A stage s = TMEM columns [tmem_a0 + s*a_stage_cols, +UMMAS*8), B stage s in shared
+// memory at smem_saddr + s*stage_bytes. Same warp-uniform structure as mma_issue_loop.
+template <int UMMAS>
+__device__ __forceinline__ void mma_issue_loop_ts(uint32_t tmem_d, uint32_t tmem_a0, uint32_t a_stage_cols, uint32_t idesc,
+                                                  uint32_t smem_saddr, uint32_t stage_bytes, OperandDesc b,
+                                                  uint32_t full_saddr, uint32_t empty_saddr, uint32_t tmem_full_saddr,
+                                                  int stages, int nkb) {
+  const uint32_t b_lo0 = ((smem_saddr & 0x3FFFFu) >> 4) | ((b.lbo >> 4) << 16);
+  const uint32_t b_hi = (b.sbo >> 4) | (1u << 14) | (b.layout_type << 29);
+  const uint32_t b_step = b.k_advance >> 4, stage_step = stage_bytes >> 4;
+  uint32_t ta = tmem_a0, b_lo = b_lo0, fb = full_saddr, eb = empty_saddr, ph = 0, acc = 0;
+  int s = 0;
+#pragma unroll 1
+  for (int i = 0; i < nkb; ++i) {
+    mbar_wait_addr(fb, ph);
+    tc_fence_after();
+    if (elect_one()) {
+#pragma unroll
+      for (int k = 0; k < UMMAS; ++k) umma_tf32_ts(tmem_d, ta + k * 8u, b_lo + k * b_step, b_hi, idesc, k ? 1u : acc);
+      umma_commit_addr(eb);               // frees the TMEM A stage and the smem B stage when these MMAs retire
+    }
+    acc = 1u;
+    if (++s == stages) {
+      s = 0; ph ^= 1u; ta = tmem_a0; b_lo = b_lo0; fb = full_saddr; eb = empty_saddr;
+    } else {
+      ta += a_stage_cols; b_lo += stage_step; fb += 8u; eb += 8u;
+    }
+  }
+  if (elect_one()) umma_commit_addr(tmem_full_saddr);
+  __syncwarp();
+}
+
 }  // namespace tc
 }  // namespace b200
