@@ -137,6 +137,14 @@ int b200ddp_conv2d_wgrad(const float* x, const float* dy, float* dw, const int* 
  * matrices with the reduction index in channel-block-major order (k_order 1). */
 int b200ddp_conv2d_weight_prep(const float* w, float* out, int Cout, int Cin, int KH, int KW, long long ld_out, int mode,
                                int device, void* stream);
+/* mode 4 | S << 8: forward weights for the space-to-depth form of a stride-S convolution (Cin*S*S <= 64): the
+ * equivalent stride-1 kernel with ceil(KH/S) x ceil(KW/S) taps over 64 channels c' = (ci*S + a)*S + b,
+ * w'[co][c'][q][r] = w[co][ci][S*q + a][S*r + b], channel-block-major; ld_out >= 64*ceil(KH/S)*ceil(KW/S). */
+/* out[n][(c*S + a)*S + b][i][j] = x[n][c][S*i + a - pad][S*j + b - pad] (0 elsewhere; out: [Nb][Cp][Hs][Ws], Cp >=
+ * C*S*S, zeroed once by the caller - positions no input maps to are never written). Input transform of the first
+ * layer: the stride-4 11x11 convolution over 3 channels (alexnet.py:22) becomes a stride-1 3x3 over 48(64). */
+int b200ddp_space_to_depth(const float* x, float* out, int Nb, int C, int H, int W, int S, int pad, int Cp, int Hs, int Ws,
+                           int device, void* stream);
 /* Several weight_prep jobs in one launch (at most 16): what a training step needs for all conv layers at once. */
 typedef struct b200ddp_weight_prep_job {
   const float* w;      /* [Cout][Cin][KH][KW] */

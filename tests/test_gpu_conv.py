@@ -137,6 +137,39 @@ def test_conv_relu_pool_fused_module_matches_float64(layer):
         assert _err(x.grad, x2.grad) < TOL
 
 
+def test_space_to_depth_and_its_weight_form_exact():
+    """b200ddp_space_to_depth + weight_prep mode 4|S<<8 against torch: pad -> pixel_unshuffle(4) for the input, and
+    the stride-1 3x3 x 64-channel kernel rebuilt from the 11x11 stride-4 one; then the two convolutions agree in
+    float64 (the identity the first layer's forward relies on)."""
+    L = _lib.load()
+    st = torch.cuda.current_stream(DEV).cuda_stream
+    torch.manual_seed(11)
+    N, C, H, S, pad, KH = 3, 3, 224, 4, 2, 11
+    x = torch.randn(N, C, H, H, device=DEV)
+    OH = (H + 2 * pad - KH) // S + 1
+    KHp = (KH + S - 1) // S
+    Hs = OH + KHp - 1
+    out = torch.zeros(N, 64, Hs, Hs, device=DEV)
+    _lib.check(L.b200ddp_space_to_depth(x.data_ptr(), out.data_ptr(), N, C, H, H, S, pad, 64, Hs, Hs, 0, st), "s2d")
+    xp = torch.nn.functional.pad(x, (pad, S * Hs - H - pad, pad, S * Hs - H - pad))
+    want = torch.nn.functional.pixel_unshuffle(xp, S)          # channel index (c*S + a)*S + b
+    assert torch.equal(out[:, :C * S * S], want) and float(out[:, C * S * S:].abs().sum()) == 0
+    w = torch.randn(64, C, KH, KH, device=DEV)
+    ld = 64 * KHp * KHp
+    wm = torch.empty(64, ld, device=DEV)
+    _lib.check(L.b200ddp_conv2d_weight_prep(w.data_ptr(), wm.data_ptr(), 64, C, KH, KH, ld, 4 | (S << 8), 0, st), "prep4")
+    wpad = torch.zeros(64, C, S * KHp, S * KHp, device=DEV)
+    wpad[:, :, :KH, :KH] = w
+    # w'[co][(c,a,b)][q][r] = wpad[co][c][S*q + a][S*r + b]
+    w2 = wpad.reshape(64, C, KHp, S, KHp, S).permute(0, 1, 3, 5, 2, 4).reshape(64, C * S * S, KHp, KHp)
+    w2 = torch.cat([w2, torch.zeros(64, 64 - C * S * S, KHp, KHp, device=DEV)], 1)
+    want_m = w2.reshape(64, 2, 32, KHp * KHp).permute(0, 1, 3, 2).reshape(64, ld)     # channel-block-major
+    assert torch.equal(wm, want_m)
+    y_direct = torch.nn.functional.conv2d(x.double(), w.double(), stride=S, padding=pad)
+    y_s2d = torch.nn.functional.conv2d(out.double(), w2.double())
+    assert y_direct.shape == y_s2d.shape and float((y_direct - y_s2d).abs().max()) < 1e-9
+
+
 def test_weight_prep_and_channel_sum_exact():
     L = _lib.load()
     st = torch.cuda.current_stream(DEV).cuda_stream

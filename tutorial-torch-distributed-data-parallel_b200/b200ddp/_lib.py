@@ -69,6 +69,7 @@ _PROTOS = {
     "b200ddp_conv2d_wgrad": (c_int, [_P, _P, _P, _P, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int,
                                      _P, c_longlong, c_int, _P]),
     "b200ddp_conv2d_weight_prep": (c_int, [_P, _P, c_int, c_int, c_int, c_int, c_longlong, c_int, c_int, _P]),
+    "b200ddp_space_to_depth": (c_int, [_P, _P, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, _P]),
     "b200ddp_conv2d_weight_prep_multi": (c_int, [POINTER(WeightPrepJob), c_int, c_int, _P]),
     "b200ddp_channel_sum_scratch_bytes": (c_longlong, [c_int, c_int]),
     "b200ddp_channel_sum": (c_int, [_P, _P, c_int, c_int, c_int, _P, c_longlong, c_int, _P]),

@@ -13,6 +13,8 @@ from __future__ import annotations
 
 from typing import Optional
 
+import os
+
 import torch
 import torch.distributed as dist
 from torch import nn
@@ -201,6 +203,49 @@ def conv_weight_matrix(w, mode: int):
     return out, ld
 
 
+def _use_s2d(Cin: int, KH: int, KW: int, stride: int) -> bool:
+    """Space-to-depth form of a strided convolution over few channels (the toy model's first layer)."""
+    if os.environ.get("B200DDP_CONV1_S2D", "0") != "1":
+        return False
+    return 2 <= stride <= 8 and Cin * stride * stride <= 64 and KH == KW and KH > stride
+
+
+_S2D_BUFS = {}
+
+
+def _s2d_geometry(H: int, W: int, KH: int, KW: int, stride: int, pad: int):
+    OH, OW = (H + 2 * pad - KH) // stride + 1, (W + 2 * pad - KW) // stride + 1
+    KHp, KWp = (KH + stride - 1) // stride, (KW + stride - 1) // stride
+    return OH, OW, KHp, KWp, OH + KHp - 1, OW + KWp - 1
+
+
+def _conv_forward_s2d(x, w, bias, stride, pad, relu, prepared):
+    """y = conv(x, w) through b200ddp_space_to_depth + the channel-block-major stride-1 kernel."""
+    L = _lib.load()
+    N, Cin, H, W = x.shape
+    Cout, _, KH, KW = w.shape
+    OH, OW, KHp, KWp, Hs, Ws = _s2d_geometry(H, W, KH, KW, stride, pad)
+    key = (str(x.device), N, Cin, H, W, stride, pad, KH, KW)
+    xs = _S2D_BUFS.get(key)
+    if xs is None:       # zeroed once: the kernel never writes the border / the channels beyond Cin*S*S
+        xs = torch.zeros((N, 64, Hs, Ws), dtype=torch.float32, device=x.device)
+        _S2D_BUFS.clear()
+        _S2D_BUFS[key] = xs
+    dev, st = _lib.dev_index(x), _lib.cur_stream(x.device)
+    _lib.check(L.b200ddp_space_to_depth(x.data_ptr(), xs.data_ptr(), N, Cin, H, W, stride, pad, 64, Hs, Ws, dev, st),
+               "space_to_depth")
+    if prepared is not None and "fwd_s2d" in prepared:
+        wmat, ldw = prepared["fwd_s2d"]
+    else:
+        ldw = 64 * KHp * KWp
+        wmat = torch.empty((Cout, ldw), dtype=torch.float32, device=w.device)
+        _lib.check(L.b200ddp_conv2d_weight_prep(w.data_ptr(), wmat.data_ptr(), Cout, Cin, KH, KW, ldw, 4 | (stride << 8),
+                                                dev, st), "weight_prep(s2d)")
+    y = conv2d_forward_raw(xs, wmat, ldw, bias, Cout, KHp, KWp, 1, 0, relu, 1)
+    assert y.shape[-2:] == (OH, OW)
+    return y
+
+
 class _Conv2dFn(torch.autograd.Function):
     """conv (+bias) [+ReLU in the epilogue] [+ReLU + 3x3/2 max pool]. Backward: the pool / ReLU backward kernel also
     produces the bias gradient (sum of the conv output gradient over batch and plane), then wgrad and dgrad."""
@@ -216,16 +261,22 @@ class _Conv2dFn(torch.autograd.Function):
         K = Cin * KH * KW
         ko = _k_order(Cin)
         ctx.dgrad_weights = None
-        if prepared is not None:      # GEMM copies made by prepare_conv_weights() for this forward/backward pair
+        if _use_s2d(Cin, KH, KW, stride):
+            # few input channels + stride S (conv1): space-to-depth turns it into a stride-1 ceil(K/S)^2 convolution
+            # over 64 channels whose gather reads consecutive pixels; the backward (wgrad) keeps the original x
+            y = _conv_forward_s2d(x, w, bias, stride, pad, relu and not pool, prepared)
+        elif prepared is not None:      # GEMM copies made by prepare_conv_weights() for this forward/backward pair
             wmat, ldw = prepared["fwd"]
             ctx.dgrad_weights = prepared.get("dgrad")
-        elif ko == 1:
-            wmat, ldw = conv_weight_matrix(w, 2)
-        elif K % 4 == 0 and w.data_ptr() % 16 == 0:
-            wmat, ldw = w, K
-        else:   # TMA needs 16-byte aligned rows: zero-padded copy (conv1: K = 363)
-            wmat, ldw = conv_weight_matrix(w, 0)
-        y = conv2d_forward_raw(x, wmat, ldw, bias, Cout, KH, KW, stride, pad, relu and not pool, ko)
+            y = conv2d_forward_raw(x, wmat, ldw, bias, Cout, KH, KW, stride, pad, relu and not pool, ko)
+        else:
+            if ko == 1:
+                wmat, ldw = conv_weight_matrix(w, 2)
+            elif K % 4 == 0 and w.data_ptr() % 16 == 0:
+                wmat, ldw = w, K
+            else:   # TMA needs 16-byte aligned rows: zero-padded copy
+                wmat, ldw = conv_weight_matrix(w, 0)
+            y = conv2d_forward_raw(x, wmat, ldw, bias, Cout, KH, KW, stride, pad, relu and not pool, ko)
         ctx.stride, ctx.pad, ctx.relu, ctx.pool = stride, pad, relu, pool
         ctx.weight_param, ctx.bias_param = weight, bias
         if pool:
@@ -335,7 +386,13 @@ class Conv2d(nn.Conv2d):
                 t = torch.empty((rows, ld), dtype=torch.float32, device=w.device)
                 self._prep_bufs[tag] = t
             return t
-        if _k_order(Cin) == 1:
+        if _use_s2d(Cin, KH, KW, self.stride[0]):
+            S = self.stride[0]
+            ld = 64 * ((KH + S - 1) // S) * ((KW + S - 1) // S)
+            out = buf("fwd_s2d", Cout, ld)
+            jobs.append((w, out, 4 | (S << 8), ld))
+            prepared["fwd_s2d"] = (out, ld)
+        elif _k_order(Cin) == 1:
             out = buf("fwd", Cout, K)
             jobs.append((w, out, 2, K))
             prepared["fwd"] = (out, K)

@@ -42,9 +42,6 @@ using namespace tc;
 constexpr int CBM = 128;            // UMMA_M
 constexpr int CBK = 32;             // fp32 per k-block (128 bytes)
 constexpr int CUK = 8;              // K per tcgen05.mma kind::tf32
-constexpr int kGroups = 3;          // forward / dgrad: 3 producer groups x 32 loads in flight per thread
-constexpr int kProdWarps = 4 * kGroups;
-constexpr int kConvThreads = 32 * (kProdWarps + 2);   // producer/epilogue warps + MMA warp (+ TMEM alloc) + weight-TMA warp
 constexpr int kWgGroups = 3;        // wgrad: 3 producer groups, batches of 32 loads software-pipelined in registers
 constexpr int kWgProdWarps = 4 * kWgGroups;
 constexpr int kWgThreads = 32 * (kWgProdWarps + 1);
@@ -100,10 +97,28 @@ struct ConvFwdParams {
 // PL: -1 = table path (k_order 0); 0 = channel-inner path with a runtime channel stride; > 0 = channel-inner path
 // with the plane size H*W known at compile time (the toy model's 27x27 and 13x13 planes), so that the 32 loads
 // of a k-block are `LDG [base + immediate]` with no address arithmetic at all.
-template <int BN, int PL>
-__global__ void __launch_bounds__(kConvThreads, 1)
+// Two shapes of CTA. Default: 3 producer groups, one CTA per SM, all 512 TMEM columns (accumulator + 8 A stages).
+// TWO: 2 producer groups and 256 TMEM columns (64-column accumulator + 6 A stages) so that two CTAs share an SM:
+// with short tiles the prologue / pipeline fill / drain / epilogue of a tile (~5 us) overlaps the other CTA's main loop.
+template <bool TWO>
+struct FwdShape {
+  static constexpr int kGroupsT = TWO ? 2 : 3;
+  static constexpr int kProdWarpsT = 4 * kGroupsT;
+  static constexpr int kThreads = 32 * (kProdWarpsT + 2);   // + MMA warp (TMEM alloc) + weight-TMA warp
+  static constexpr int kCtasPerSm = TWO ? 2 : 1;
+  static constexpr uint32_t kTmemColsT = TWO ? 256 : 512;
+  static constexpr uint32_t kATmemCol0T = TWO ? 64 : 256;
+  static constexpr int kMaxStages = TWO ? 6 : 8;
+};
+
+// TWO (only with BN == 64): the two-CTAs-per-SM shape, chosen by the host for short reduction loops (conv1 forward:
+// 18 k-blocks per tile); long loops (conv2 dgrad: 150) are faster with one CTA of three producer groups.
+template <int BN, int PL, bool TWO = false>
+__global__ void __launch_bounds__(FwdShape<TWO>::kThreads, FwdShape<TWO>::kCtasPerSm)
 conv_fwd_kernel(const __grid_constant__ CUtensorMap tmW, ConvFwdParams p) {
+  static_assert(!TWO || BN == 64, "the two-CTA shape has room for a 64-column accumulator only");
   constexpr bool CI = PL >= 0;
+  constexpr int kGroups = FwdShape<TWO>::kGroupsT, kProdWarps = FwdShape<TWO>::kProdWarpsT;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   // The im2col tile (A) goes registers -> TENSOR MEMORY (tcgen05.st), not shared memory: ncu showed the unified
@@ -112,8 +127,8 @@ conv_fwd_kernel(const __grid_constant__ CUtensorMap tmW, ConvFwdParams p) {
   // TMA-fed weight tiles. TMEM: accumulator in columns [0, BN), A stage s in [kATmemCol0 + 32 s, +32).
   constexpr uint32_t B_BYTES = BN * CBK * 4;
   constexpr uint32_t STAGE_BYTES = B_BYTES;
-  constexpr uint32_t kATmemCol0 = 256, kTmemCols = 512;
-  const int stages = p.stages;                        // <= 8 (8 x 32 A columns)
+  constexpr uint32_t kATmemCol0 = FwdShape<TWO>::kATmemCol0T, kTmemCols = FwdShape<TWO>::kTmemColsT;
+  const int stages = p.stages;                        // <= FwdShape<TWO>::kMaxStages (32 A columns each)
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + (size_t)stages * STAGE_BYTES);
   uint64_t* empty_bar = full_bar + stages;
   uint64_t* tmem_full_bar = empty_bar + stages;
@@ -531,10 +546,31 @@ __global__ void __launch_bounds__(256) wgrad_finalize_ci_kernel(const float* __r
 // mode 1: dgrad weights, k' = (co, kh', kw'):  out[ci][co*KH*KW + (KH-1-kh)*KW + (KW-1-kw)] = w[co][ci][kh][kw]
 // mode 2: forward weights, channel-block-major:  out[co][((ci/32)*KHW + kh*KW + kw)*32 + ci%32]               = w[co][ci][kh][kw]
 // mode 3: dgrad weights, channel-block-major:    out[ci][((co/32)*KHW + (KH-1-kh)*KW + (KW-1-kw))*32 + co%32] = w[co][ci][kh][kw]
+// mode 4 | S << 8: forward weights of the space-to-depth form of a stride-S convolution (see s2d_pad_kernel): the
+//         equivalent stride-1 kernel has KH' = ceil(KH/S) taps over Cp = 64 channels c' = (ci*S + a)*S + b with
+//         w'[co][c'][q][r] = w[co][ci][S*q + a][S*r + b] (0 outside the KHxKW window and for c' >= Cin*S*S), stored
+//         channel-block-major: out[co][((c'/32)*KH'*KW' + q*KW' + r)*32 + c'%32]
 __device__ __forceinline__ void weight_prep_body(const float* __restrict__ w, float* __restrict__ out, int Cout, int Cin,
                                                  int KH, int KW, long long ld_out, int mode, long long first,
                                                  long long stride) {
   const int KHW = KH * KW;
+  if ((mode & 0xff) == 4) {
+    const int S = mode >> 8, KHp = (KH + S - 1) / S, KWp = (KW + S - 1) / S, Cp = 64;
+    const int Kp = Cp * KHp * KWp;
+    const long long total = (long long)Cout * Kp;
+    for (long long i = first; i < total; i += stride) {
+      // i enumerates the OUTPUT row-major over [co][Kp]
+      const int co = (int)(i / Kp), k = (int)(i - (long long)co * Kp);
+      const int slab = k >> 5, cblk = slab / (KHp * KWp), qr = slab - cblk * (KHp * KWp);
+      const int q = qr / KWp, r = qr - q * KWp, cp = (cblk << 5) + (k & 31);
+      const int b = cp % S, a = (cp / S) % S, ci = cp / (S * S);
+      const int kh = S * q + a, kw = S * r + b;
+      float v = 0.f;
+      if (ci < Cin && kh < KH && kw < KW) v = __ldg(w + (((long long)co * Cin + ci) * KH + kh) * KW + kw);
+      out[(long long)co * ld_out + k] = v;
+    }
+    return;
+  }
   if (mode == 0) {
     const int K = Cin * KHW;
     const long long total = (long long)Cout * ld_out;
@@ -595,6 +631,37 @@ __global__ void __launch_bounds__(256) conv_weight_prep_multi_kernel(const __gri
                    (long long)nblocks * blockDim.x);
 }
 
+// Space-to-depth with padding for a stride-S convolution over few channels (conv1: 3 channels, 11x11, stride 4):
+//   out[n][(c*S + a)*S + b][i][j] = x[n][c][S*i + a - pad][S*j + b - pad]
+// turns it into a stride-1 ceil(KH/S) x ceil(KW/S) convolution over C*S*S channels, whose im2col gather reads
+// CONSECUTIVE pixels (the strided original touches four 128-byte lines per warp load). One thread per input element;
+// `out` has Cp >= C*S*S channel planes of Hs x Ws and must be zero where no input lands (zeroed once by the caller:
+// the border and the channels beyond C*S*S are never written).
+__global__ void __launch_bounds__(256) s2d_pad_kernel(const float* __restrict__ x, float* __restrict__ out, int C, int H,
+                                                      int W, int S, int pad, int Cp, int Hs, int Ws) {
+  // grid: (chunks of a plane, n*C + c). One thread per (row h, group k of S consecutive columns): it reads x[h][S*k + t],
+  // t < S, and stores element t to channel (c, a, (pad+t) % S) at column k + (pad+t) / S. Consecutive lanes are
+  // consecutive k, so every load and every one of the S stores of a warp is one contiguous run.
+  const int plane = blockIdx.y;
+  const int n = plane / C, c = plane - n * C;
+  const int Wk = (W + S - 1) / S;
+  const int per_plane = H * Wk;
+  float* op = out + (long long)n * Cp * Hs * Ws;
+  const long long cs = (long long)Hs * Ws;
+  for (int e = blockIdx.x * blockDim.x + threadIdx.x; e < per_plane; e += gridDim.x * blockDim.x) {
+    const int h = e / Wk, k = e - h * Wk;
+    const int hp = h + pad, i = hp / S, a = hp - i * S;
+    if (i >= Hs) continue;
+    const float* xr = x + ((long long)plane * H + h) * W + (long long)S * k;
+    float* orow = op + ((long long)((c * S + a) * S) * cs) + (long long)i * Ws;      // channel (c,a,0), row i
+    for (int t = 0; t < S; ++t) {
+      if (S * k + t >= W) break;
+      const int q = pad + t, dj = q / S, b = q - dj * S, j = k + dj;
+      if (j < Ws) orow[b * cs + j] = __ldg(xr + t);
+    }
+  }
+}
+
 // out[c] = sum over (n, pix) of dy[n][c][pix]  (bias gradient). S x C CTAs, deterministic last-ticket merge.
 constexpr int kCsThreads = 256;
 constexpr int kCsMaxChannels = 4096;
@@ -633,13 +700,13 @@ inline int cs_splits(int Nb, int C) {
   return s < 1 ? 1 : s;
 }
 
-template <int BN, int PL>
+template <int BN, int PL, bool TWO = false>
 int launch_fwd(const CUtensorMap& tmW, const ConvFwdParams& p, cudaStream_t stream) {
   const size_t stage_bytes = (size_t)BN * CBK * 4;       // weight tile only: the im2col tile lives in TMEM
   const size_t smem = 1024 + (size_t)p.stages * stage_bytes + (2 * p.stages + 1) * 8 + 16;
   static bool attr_set = false;
   if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(conv_fwd_kernel<BN, PL>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    cudaError_t e = cudaFuncSetAttribute(conv_fwd_kernel<BN, PL, TWO>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
     if (e != cudaSuccess) {
       set_error("cudaFuncSetAttribute(conv_fwd_kernel<%d>) -> %s", BN, cudaGetErrorString(e));
       return kCudaErrBase + (int)e;
@@ -647,7 +714,7 @@ int launch_fwd(const CUtensorMap& tmW, const ConvFwdParams& p, cudaStream_t stre
     attr_set = true;
   }
   dim3 grid((p.M + CBM - 1) / CBM, (p.Cout + BN - 1) / BN, 1);
-  conv_fwd_kernel<BN, PL><<<grid, kConvThreads, smem, stream>>>(tmW, p);
+  conv_fwd_kernel<BN, PL, TWO><<<grid, FwdShape<TWO>::kThreads, smem, stream>>>(tmW, p);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) {
     set_error("conv_fwd_kernel<%d> launch (grid %d,%d smem %zu) -> %s", BN, grid.x, grid.y, smem, cudaGetErrorString(e));
@@ -760,9 +827,12 @@ int b200ddp_conv2d_fwd(const float* x, const float* wmat, long long ldw, const f
   // ring depth: 8 A stages fit the TMEM columns left of the accumulator; the weight-tile ring is <= 8 x 32 KB,
   // which leaves >= ~90 KB of the SM array as L1 for the channel-block-major reuse
   int stages = (int)((160 * 1024) / ((size_t)bn * CBK * 4));
-  if (stages > 8) stages = 8;
+  const bool two = bn == 64 && p.kblocks <= 32;      // short tiles: two CTAs per SM
+  const int max_stages = two ? FwdShape<true>::kMaxStages : FwdShape<false>::kMaxStages;
+  const int groups = two ? FwdShape<true>::kGroupsT : FwdShape<false>::kGroupsT;
+  if (stages > max_stages) stages = max_stages;
   if (stages > p.kblocks) stages = p.kblocks;
-  if (stages < kGroups) stages = kGroups;
+  if (stages < groups) stages = groups;
   p.stages = stages;
   CUtensorMap tmW;
   int rc = tma_map_2d(&tmW, wmat, ldw, Cout, ldw, CBK, bn, 0);
@@ -777,10 +847,15 @@ int b200ddp_conv2d_fwd(const float* x, const float* wmat, long long ldw, const f
   }
   if (k_order == 1) {
     const int plane = H * W;
+    if (two) {                                                         // conv1 after space-to-depth, small test shapes
+      if (plane == 57 * 57) return launch_fwd<64, 57 * 57, true>(tmW, p, s);
+      return launch_fwd<64, 0, true>(tmW, p, s);
+    }
     if (plane == 27 * 27) { B200_FWD_BN(27 * 27) }
     if (plane == 13 * 13) { B200_FWD_BN(13 * 13) }
     B200_FWD_BN(0)
   }
+  if (two) return launch_fwd<64, -1, true>(tmW, p, s);
   B200_FWD_BN(-1)
 #undef B200_FWD_BN
 }
@@ -861,14 +936,33 @@ int b200ddp_conv2d_wgrad(const float* x, const float* dy, float* dw, const int* 
   return 0;
 }
 
+static int check_prep_mode(int Cout, int Cin, int KH, int KW, long long ld_out, int mode, const char* who) {
+  const int m = mode & 0xff, S = mode >> 8;
+  B200_CHECK_ARG(m >= 0 && m <= 4 && (m == 4 || S == 0), "%s: mode must be 0..3 or 4 | S << 8 (got %d)", who, mode);
+  if (m == 4) {
+    B200_CHECK_ARG(S >= 2 && S <= 8 && Cin * S * S <= 64, "%s: space-to-depth needs 2 <= S <= 8 and Cin*S*S <= 64", who);
+    B200_CHECK_ARG(ld_out >= 64LL * ((KH + S - 1) / S) * ((KW + S - 1) / S), "%s: ld_out too small", who);
+    return 0;
+  }
+  B200_CHECK_ARG((m == 0 || m == 2) ? ld_out >= (long long)Cin * KH * KW : ld_out >= (long long)Cout * KH * KW,
+                 "%s: ld_out too small", who);
+  return 0;
+}
+static long long prep_total(int Cout, int Cin, int KH, int KW, long long ld_out, int mode) {
+  if ((mode & 0xff) == 4) {
+    const int S = mode >> 8;
+    return (long long)Cout * 64 * ((KH + S - 1) / S) * ((KW + S - 1) / S);
+  }
+  return mode == 0 ? (long long)Cout * ld_out : (long long)Cout * Cin * KH * KW;
+}
+
 int b200ddp_conv2d_weight_prep(const float* w, float* out, int Cout, int Cin, int KH, int KW, long long ld_out, int mode,
                                int device, void* stream) {
   B200_CHECK_ARG(w && out && Cout > 0 && Cin > 0 && KH > 0 && KW > 0, "conv2d_weight_prep: bad argument");
-  B200_CHECK_ARG(mode >= 0 && mode <= 3, "conv2d_weight_prep: mode must be 0..3");
-  B200_CHECK_ARG((mode == 0 || mode == 2) ? ld_out >= (long long)Cin * KH * KW : ld_out >= (long long)Cout * KH * KW,
-                 "conv2d_weight_prep: ld_out too small");
+  const int rc_mode = check_prep_mode(Cout, Cin, KH, KW, ld_out, mode, "conv2d_weight_prep");
+  if (rc_mode) return rc_mode;
   B200_DEVICE(device);
-  const long long total = mode == 0 ? (long long)Cout * ld_out : (long long)Cout * Cin * KH * KW;
+  const long long total = prep_total(Cout, Cin, KH, KW, ld_out, mode);
   long long want = (total + 255) / 256;
   const int grid = (int)(want < kNumSMs * 8 ? (want < 1 ? 1 : want) : kNumSMs * 8);
   conv_weight_prep_kernel<<<grid, 256, 0, as_stream(stream)>>>(w, out, Cout, Cin, KH, KW, ld_out, mode);
@@ -884,11 +978,9 @@ int b200ddp_conv2d_weight_prep_multi(const b200ddp_weight_prep_job* jobs, int nj
   for (int j = 0; j < njobs; ++j) {
     const b200ddp_weight_prep_job& q = jobs[j];
     B200_CHECK_ARG(q.w && q.out && q.Cout > 0 && q.Cin > 0 && q.KH > 0 && q.KW > 0, "conv2d_weight_prep_multi: job %d: bad argument", j);
-    B200_CHECK_ARG(q.mode >= 0 && q.mode <= 3, "conv2d_weight_prep_multi: job %d: mode must be 0..3", j);
-    B200_CHECK_ARG((q.mode == 0 || q.mode == 2) ? q.ld_out >= (long long)q.Cin * q.KH * q.KW
-                                                : q.ld_out >= (long long)q.Cout * q.KH * q.KW,
-                   "conv2d_weight_prep_multi: job %d: ld_out too small", j);
-    const long long total = q.mode == 0 ? (long long)q.Cout * q.ld_out : (long long)q.Cout * q.Cin * q.KH * q.KW;
+    const int rc_mode = check_prep_mode(q.Cout, q.Cin, q.KH, q.KW, q.ld_out, q.mode, "conv2d_weight_prep_multi");
+    if (rc_mode) return rc_mode;
+    const long long total = prep_total(q.Cout, q.Cin, q.KH, q.KW, q.ld_out, q.mode);
     long long want = (total + 1023) / 1024;                      // ~4 elements per thread
     if (want < 1) want = 1;
     if (want > kNumSMs * 4) want = kNumSMs * 4;
@@ -899,6 +991,18 @@ int b200ddp_conv2d_weight_prep_multi(const b200ddp_weight_prep_job* jobs, int nj
   J.first_block[njobs] = blocks;
   B200_DEVICE(device);
   conv_weight_prep_multi_kernel<<<blocks, 256, 0, as_stream(stream)>>>(J);
+  B200_LAUNCH_OK();
+  return 0;
+}
+
+int b200ddp_space_to_depth(const float* x, float* out, int Nb, int C, int H, int W, int S, int pad, int Cp, int Hs, int Ws,
+                           int device, void* stream) {
+  B200_CHECK_ARG(x && out && Nb > 0 && C > 0 && H > 0 && W > 0, "space_to_depth: bad argument");
+  B200_CHECK_ARG(S >= 2 && S <= 8 && pad >= 0 && Cp >= C * S * S && Hs > 0 && Ws > 0, "space_to_depth: bad geometry");
+  B200_DEVICE(device);
+  B200_CHECK_ARG((long long)Nb * C <= 65535 && (long long)H * W < (1LL << 30), "space_to_depth: tensor too large");
+  const int per_plane = H * ((W + S - 1) / S);
+  s2d_pad_kernel<<<dim3((per_plane + 1023) / 1024, Nb * C), 256, 0, as_stream(stream)>>>(x, out, C, H, W, S, pad, Cp, Hs, Ws);
   B200_LAUNCH_OK();
   return 0;
 }
