@@ -30,6 +30,10 @@ int b200ddp_version(void);
 /* Number of CUDA kernels this library has launched in this process (evidence for bench `gpu_launches`). */
 unsigned long long b200ddp_launch_count(void);
 int b200ddp_device_info(int device, int* sm_count, int* cc_major, int* cc_minor);
+/* Number of SMs the grid planners (split counts of the wgrad and GEMM kernels) may assume are free; 0 or > 148 = all.
+ * Returns the previous value. The DDP wrapper lowers it by the number of NCCL channels: an all-reduce that is
+ * resident on 8 SMs turns a 148-CTA one-wave grid into two waves (measured: 2-GPU step 4.2 ms instead of 2.9 ms). */
+int b200ddp_set_sm_budget(int sms);
 
 /* ---- O1: optimizer ---------------------------------------------------------------------------- */
 /* Replaces torch.optim.Adam._multi_tensor_adam (torch/optim/adam.py:554-800), reached from

@@ -6,7 +6,15 @@ annalena-k/tutorial-torch-distributed-data-parallel, behind the surface the tuto
     from b200ddp.accelerate import Accelerator                                # multi-GPU-training-accelerate.py:19
     from b200ddp.models import load_model                                     # data_and_toy_model.py:41-45
 """
-from . import _lib, nn, optim  # noqa: F401
+import os as _os
+
+# The gradient all-reduce runs concurrently with the convolution backward; NCCL's persistent kernel owns one SM per
+# channel for its whole duration. Capping the channels (8 move 228 MB well inside the backward on NVLink 5) and
+# planning one-wave grids for the remaining SMs (b200ddp_set_sm_budget, see comm.py) keeps both sides at full speed.
+# Must be in the environment before the first NCCL communicator of the process is created.
+_os.environ.setdefault("NCCL_MAX_NCHANNELS", "8")
+
+from . import _lib, nn, optim  # noqa: F401,E402
 from .arena import FlatArena  # noqa: F401
 from .distributed import DistributedDataParallel  # noqa: F401
 from .nn import CrossEntropyLoss, SyncBatchNorm  # noqa: F401

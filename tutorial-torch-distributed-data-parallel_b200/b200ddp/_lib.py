@@ -35,6 +35,7 @@ _PROTOS = {
     "b200ddp_last_error": (c_char_p, []),
     "b200ddp_version": (c_int, []),
     "b200ddp_launch_count": (c_ulonglong, []),
+    "b200ddp_set_sm_budget": (c_int, [c_int]),
     "b200ddp_device_info": (c_int, [c_int, POINTER(c_int), POINTER(c_int), POINTER(c_int)]),
     "b200ddp_adam_step_flat": (c_int, [_P, _P, _P, _P, c_longlong, c_double, c_double, c_double, c_double, c_double,
                                        c_longlong, _P, c_int, _P]),

@@ -8,6 +8,7 @@ the C library on its own communication stream (include/b200ddp.h, R4).
 from __future__ import annotations
 
 import atexit
+import os
 import ctypes
 from typing import Dict, Optional
 
@@ -88,6 +89,12 @@ def get_comm(device: torch.device, process_group=None) -> Optional[NativeComm]:
     _lib.check(L.b200ddp_comm_create(ctypes.byref(handle), uid, rank, world, dev_index), "comm_create")
     comm = NativeComm(handle.value, rank, world, device)
     _COMMS[key] = comm
+    # leave the SMs of the collective's channels out of the one-wave grid plans (see b200ddp/__init__.py)
+    try:
+        channels = int(os.environ.get("NCCL_MAX_NCHANNELS", "8"))
+    except ValueError:
+        channels = 8
+    L.b200ddp_set_sm_budget(148 - max(0, min(channels, 32)))
     return comm
 
 

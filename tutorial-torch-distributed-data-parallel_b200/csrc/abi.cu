@@ -10,6 +10,7 @@ namespace b200 {
 
 static thread_local char g_err[1024] = "";
 std::atomic<unsigned long long> g_launches{0};
+std::atomic<int> g_sm_budget{kNumSMs};
 
 void set_error(const char* fmt, ...) {
   va_list ap;
@@ -27,6 +28,14 @@ const char* b200ddp_last_error(void) { return b200::g_err; }
 int b200ddp_version(void) { return 100; }
 
 unsigned long long b200ddp_launch_count(void) { return b200::g_launches.load(); }
+
+int b200ddp_set_sm_budget(int sms) {
+  const int prev = b200::g_sm_budget.load();
+  if (sms <= 0 || sms > b200::kNumSMs) sms = b200::kNumSMs;
+  if (sms < 16) sms = 16;
+  b200::g_sm_budget.store(sms);
+  return prev;
+}
 
 int b200ddp_device_info(int device, int* sm_count, int* cc_major, int* cc_minor) {
   cudaDeviceProp prop;

@@ -30,6 +30,9 @@ enum : int {
 
 void set_error(const char* fmt, ...);
 extern std::atomic<unsigned long long> g_launches;
+// SMs the grid planners may count on (b200ddp_set_sm_budget): all 148 unless a resident collective owns some.
+extern std::atomic<int> g_sm_budget;
+inline int sm_budget() { return g_sm_budget.load(std::memory_order_relaxed); }
 
 inline void count_launch(int n = 1) { g_launches.fetch_add((unsigned long long)n, std::memory_order_relaxed); }
 

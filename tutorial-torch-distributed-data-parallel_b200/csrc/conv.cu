@@ -777,9 +777,9 @@ inline WgradPlan plan_wgrad(int Nb, int Cin, int OH, int OW, int Cout, int KH, i
   w.n_tiles = (Cout + w.bn - 1) / w.bn;
   const long long M = (long long)Nb * OH * OW;
   w.kblocks_total = (int)((M + CBK - 1) / CBK);
-  int splits = kNumSMs / (w.m_tiles * w.n_tiles);
+  int splits = sm_budget() / (w.m_tiles * w.n_tiles);
   if (splits < 1) splits = 1;
-  if (splits > kNumSMs) splits = kNumSMs;
+  if (splits > sm_budget()) splits = sm_budget();
   if (splits > w.kblocks_total) splits = w.kblocks_total;
   w.per = (w.kblocks_total + splits - 1) / splits;
   w.splits = (w.kblocks_total + w.per - 1) / w.per;

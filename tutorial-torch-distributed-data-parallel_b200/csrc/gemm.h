@@ -51,6 +51,12 @@ int tf32_gemm_launch(const float* A, long long lda, int a_mn_major, const float*
 int tma_map_2d(CUtensorMap* map, const float* base, long long inner, long long outer, long long ld, int box_inner,
                int box_outer, int swizzle_base32b);
 
+// 128-row sub-tiles per CTA that tf32_gemm_launch uses for an M x N x R problem. The kernel supports 2 (two TMEM
+// accumulators sharing one B tile, parity-tested), but on the classifier GEMMs it measured SLOWER than 1
+// (FC1 forward 57 vs 50 us, dX 53 vs 47 us on B200): those kernels are bound by the per-SM TMA fill rate
+// (~26 B/clk/SM whatever the tile shape), not by L2->SM traffic, so fewer, fatter CTAs only lose parallelism.
+inline int tf32_row_subtiles(int M, int R) { (void)M; (void)R; return 1; }
+
 // Number of K splits tf32_gemm_launch will really use for a request (no empty splits).
 inline int tf32_effective_splits(int R, int splits) {
   const int total_kb = (R + 31) / 32;

@@ -48,14 +48,19 @@ struct KParams {
 
 // EPI = false: raw accumulator store (split-K partials, dgrad, wgrad) — no epilogue code is compiled in.
 // EPI = true : bias / ReLU / Philox dropout / gate byte applied while the tile leaves TMEM.
-template <int BN, bool EPI>
+// RS = 128-row sub-tiles of the output per CTA (two accumulators in TMEM share one B tile): in the classifier GEMMs the
+// M side is the streamed weight matrix and the B tile (activations) is re-read from L2 by every CTA - at RS = 1 that
+// doubles the L2->SM traffic of each streamed weight byte (the measured L2 cap, not HBM, bounded those kernels).
+template <int BN, bool EPI, int RS>
 __global__ void __launch_bounds__(kThreads)
 tf32_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, KParams p) {
   extern __shared__ uint8_t smem_raw[];
   // 1024-byte alignment is required by the 128B swizzle pattern (TMA and UMMA must agree on it).
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  constexpr uint32_t A_BYTES = BM * BK * 4;   // 16 KB
+  constexpr uint32_t A_SUB_BYTES = BM * BK * 4;   // 16 KB
+  constexpr uint32_t A_BYTES = RS * A_SUB_BYTES;
   constexpr uint32_t B_BYTES = BN * BK * 4;
+  constexpr uint32_t TMEM_COLS = RS * BN;         // 64, 128 or 256: powers of two
   constexpr uint32_t STAGE_BYTES = A_BYTES + B_BYTES;
   const int stages = p.stages;
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + (size_t)stages * STAGE_BYTES);
@@ -64,7 +69,7 @@ tf32_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full_bar + 1);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int m0 = blockIdx.x * BM, n0 = blockIdx.y * BN, z = blockIdx.z;
+  const int m0 = blockIdx.x * (BM * RS), n0 = blockIdx.y * BN, z = blockIdx.z;
   // Split-K is INTERLEAVED: split z owns k-blocks z, z+splits, z+2*splits, ... so that the CTAs working on the
   // same rows of the streamed operand touch adjacent 128-byte pieces at the same time (DRAM page locality)
   // instead of 'splits' far-apart column ranges.
@@ -80,7 +85,7 @@ tf32_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tmA) : "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tmB) : "memory");
   }
-  if (warp == 1) tmem_alloc(tmem_slot, BN);
+  if (warp == 1) tmem_alloc(tmem_slot, TMEM_COLS);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -97,10 +102,11 @@ tf32_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       uint8_t* sb = sa + A_BYTES;
       const int r0 = (z + i * p.splits) * BK;
       if (!p.a_mn) {
-        tma_load_2d(sa, &tmA, &full_bar[s], r0, m0);                       // box {32 r, 128 m}
+#pragma unroll
+        for (int j = 0; j < RS; ++j) tma_load_2d(sa + j * A_SUB_BYTES, &tmA, &full_bar[s], r0, m0 + j * BM);  // box {32 r, 128 m}
       } else {
 #pragma unroll
-        for (int j = 0; j < BM / 32; ++j) tma_load_2d(sa + j * 4096, &tmA, &full_bar[s], m0 + 32 * j, r0);  // box {32 m, 32 r}
+        for (int j = 0; j < RS * BM / 32; ++j) tma_load_2d(sa + j * 4096, &tmA, &full_bar[s], m0 + 32 * j, r0);  // box {32 m, 32 r}
       }
       if (!p.b_mn) {
         tma_load_2d(sb, &tmB, &full_bar[s], r0, n0);                       // box {32 r, BN n}
@@ -115,25 +121,26 @@ tf32_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                            | (2u << 7) | (2u << 10)       // A, B format = TF32
                            | ((uint32_t)p.a_mn << 15) | ((uint32_t)p.b_mn << 16)
                            | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
-    mma_issue_loop<BK / UMMA_K>(tmem_base, idesc, smem_u32(smem), STAGE_BYTES, A_BYTES,
-                                p.a_mn ? operand_mn_major() : operand_k_major(),
-                                p.b_mn ? operand_mn_major() : operand_k_major(), smem_u32(&full_bar[0]),
-                                smem_u32(&empty_bar[0]), smem_u32(tmem_full_bar), stages, nkb);
+    mma_issue_loop<BK / UMMA_K, RS>(tmem_base, idesc, smem_u32(smem), STAGE_BYTES, A_BYTES,
+                                    p.a_mn ? operand_mn_major() : operand_k_major(),
+                                    p.b_mn ? operand_mn_major() : operand_k_major(), smem_u32(&full_bar[0]),
+                                    smem_u32(&empty_bar[0]), smem_u32(tmem_full_bar), stages, nkb, nullptr, A_SUB_BYTES, BN);
   } else if (warp >= 2) {
     // ---------------- epilogue: TMEM -> registers -> global ----------------
     mbar_wait(tmem_full_bar, 0);
     tc_fence_after();
     const int q = warp & 3;                              // TMEM lane quarter this warp may touch
-    const int m = m0 + q * 32 + lane;
-    const bool m_ok = m < p.M;
     float* dst;
     long long ld;
     if (p.splits > 1) { dst = p.ws + (size_t)z * (size_t)p.N * (size_t)p.M; ld = p.M; }
     else { dst = p.out; ld = p.ldo; }
 #pragma unroll 1
-    for (int c = 0; c < BN; c += 32) {
+    for (int cc = 0; cc < RS * BN; cc += 32) {
+      const int sub = cc / BN, c = cc - sub * BN;          // accumulator `sub` = rows m0 + sub*128 ..
+      const int m = m0 + sub * BM + q * 32 + lane;
+      const bool m_ok = m < p.M;
       uint32_t r[32];
-      tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c, r);
+      tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)cc, r);
       if (m_ok) {
 #pragma unroll
         for (int j = 0; j < 32; ++j) {
@@ -149,7 +156,7 @@ tf32_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 1) tmem_dealloc(tmem_base, BN);
+  if (warp == 1) tmem_dealloc(tmem_base, TMEM_COLS);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -198,21 +205,21 @@ int tma_map_2d(CUtensorMap* map, const float* base, long long inner, long long o
 
 namespace {
 
-template <int BN, bool EPI>
+template <int BN, bool EPI, int RS>
 int launch_bn(const CUtensorMap& tmA, const CUtensorMap& tmB, const KParams& p, cudaStream_t stream) {
-  const size_t stage_bytes = (size_t)(BM + BN) * BK * 4;
+  const size_t stage_bytes = (size_t)(BM * RS + BN) * BK * 4;
   const size_t smem = 1024 + (size_t)p.stages * stage_bytes + (2 * p.stages + 1) * 8 + 16;
   static bool attr_set = false;   // per template instance; benign race (idempotent)
   if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(tf32_gemm_kernel<BN, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    cudaError_t e = cudaFuncSetAttribute(tf32_gemm_kernel<BN, EPI, RS>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
     if (e != cudaSuccess) {
       set_error("cudaFuncSetAttribute(tf32_gemm_kernel) -> %s", cudaGetErrorString(e));
       return kCudaErrBase + (int)e;
     }
     attr_set = true;
   }
-  dim3 grid((p.M + BM - 1) / BM, (p.N + BN - 1) / BN, p.splits);
-  tf32_gemm_kernel<BN, EPI><<<grid, kThreads, smem, stream>>>(tmA, tmB, p);
+  dim3 grid((p.M + BM * RS - 1) / (BM * RS), (p.N + BN - 1) / BN, p.splits);
+  tf32_gemm_kernel<BN, EPI, RS><<<grid, kThreads, smem, stream>>>(tmA, tmB, p);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) {
     set_error("tf32_gemm_kernel<%d> launch (grid %d,%d,%d smem %zu) -> %s", BN, grid.x, grid.y, grid.z, smem,
@@ -247,7 +254,8 @@ int tf32_gemm_launch(const float* A, long long lda, int a_mn, const float* B, lo
   p.M = M; p.N = N; p.R = R;
   p.kblocks_per_split = (total_kb + splits - 1) / splits;
   p.splits = (total_kb + p.kblocks_per_split - 1) / p.kblocks_per_split;   // no empty splits
-  const int max_stages = (BN == 128) ? 6 : 8;
+  const int rs = tf32_row_subtiles(M, R);
+  const int max_stages = (int)((200 * 1024) / ((size_t)(BM * rs + BN) * BK * 4)) > 8 ? 8 : (int)((200 * 1024) / ((size_t)(BM * rs + BN) * BK * 4));
   p.stages = p.kblocks_per_split < max_stages ? p.kblocks_per_split : max_stages;
   // short K loops (wgrad: K = batch): 2 stages keep the CTA at ~64 KB so 3 CTAs share an SM and one
   // CTA's epilogue overlaps its neighbours' loads and MMAs
@@ -260,8 +268,12 @@ int tf32_gemm_launch(const float* A, long long lda, int a_mn, const float* B, lo
     return kInvalidArg;
   }
   const bool epi = p.splits == 1 && (ep.bias || ep.relu || ep.dropout || ep.gate);
-  if (BN == 128) return epi ? launch_bn<128, true>(tmA, tmB, p, stream) : launch_bn<128, false>(tmA, tmB, p, stream);
-  return epi ? launch_bn<64, true>(tmA, tmB, p, stream) : launch_bn<64, false>(tmA, tmB, p, stream);
+  if (rs == 2) {
+    if (BN == 128) return epi ? launch_bn<128, true, 2>(tmA, tmB, p, stream) : launch_bn<128, false, 2>(tmA, tmB, p, stream);
+    return epi ? launch_bn<64, true, 2>(tmA, tmB, p, stream) : launch_bn<64, false, 2>(tmA, tmB, p, stream);
+  }
+  if (BN == 128) return epi ? launch_bn<128, true, 1>(tmA, tmB, p, stream) : launch_bn<128, false, 1>(tmA, tmB, p, stream);
+  return epi ? launch_bn<64, true, 1>(tmA, tmB, p, stream) : launch_bn<64, false, 1>(tmA, tmB, p, stream);
 }
 
 }  // namespace b200

@@ -224,9 +224,10 @@ static inline int sgemm_effective_splits(int R, int splits) {
 
 // pick a split count so that tiles * splits fits in ONE wave of 148 SMs (a 149th CTA would double the
 // kernel time: these kernels run one CTA per SM), keeping >= 128 of K per split
+constexpr int kMaxSplits = 16;
 static inline int pick_splits(int tiles, int R) {
-  int s = kNumSMs / tiles;
-  if (s > 8) s = 8;
+  int s = sm_budget() / tiles;
+  if (s > kMaxSplits) s = kMaxSplits;
   const int max_by_k = R / 128 > 0 ? R / 128 : 1;
   if (s > max_by_k) s = max_by_k;
   return s < 1 ? 1 : s;
@@ -365,9 +366,9 @@ using namespace b200;
 extern "C" {
 
 long long b200ddp_linear_workspace_bytes(int B, int N, int K) {
-  // split-K partials: at most 8 slices of the largest of the forward ([B x N]) and dgrad ([B x K]) outputs.
+  // split-K partials: at most kMaxSplits slices of the largest of the forward ([B x N]) and dgrad ([B x K]) outputs.
   const long long a = (long long)B * N, b = (long long)B * K;
-  return 8ll * (a > b ? a : b) * 4ll;
+  return (long long)kMaxSplits * (a > b ? a : b) * 4ll;
 }
 
 int b200ddp_linear_fwd(const float* x, const float* w, const float* bias, float* y, unsigned char* gate, int B, int N,
@@ -385,7 +386,7 @@ int b200ddp_linear_fwd(const float* x, const float* w, const float* bias, float*
   }
   const Epilogue ep = make_epilogue(bias, relu, dropout_p, seed, gate);
   if (mode == 1) {
-    const int tiles = ceil_div(N, 128) * ceil_div(B, 128);
+    const int tiles = ceil_div(N, 128 * tf32_row_subtiles(N, K)) * ceil_div(B, 128);
     const int splits = tf32_effective_splits(K, pick_splits(tiles, K));
     B200_CHECK_ARG(splits == 1 || (ws && ws_bytes >= (long long)splits * B * N * 4), "linear_fwd: workspace too small");
     int rc = tf32_gemm_launch(w, K, 0, x, K, 0, /*M=*/N, /*N=*/B, /*R=*/K, y, N, splits, (float*)ws, ep, s);
@@ -414,7 +415,7 @@ int b200ddp_linear_bwd_dx(const float* dz, const float* w, float* dx, int B, int
   }
   Epilogue ep;
   if (mode == 1) {
-    const int tiles = ceil_div(K, 128) * ceil_div(B, 128);
+    const int tiles = ceil_div(K, 128 * tf32_row_subtiles(K, N)) * ceil_div(B, 128);
     const int splits = tf32_effective_splits(N, pick_splits(tiles, N));
     B200_CHECK_ARG(splits == 1 || (ws && ws_bytes >= (long long)splits * B * K * 4), "linear_bwd_dx: workspace too small");
     // D[m=k][n=b] = sum_f W[f][k] * dZ[b][f]
