@@ -91,9 +91,9 @@ def get_comm(device: torch.device, process_group=None) -> Optional[NativeComm]:
     _COMMS[key] = comm
     # leave the SMs of the collective's channels out of the one-wave grid plans (see b200ddp/__init__.py)
     try:
-        channels = int(os.environ.get("NCCL_MAX_NCHANNELS", "8"))
+        channels = int(os.environ.get("NCCL_MAX_NCHANNELS", "16"))
     except ValueError:
-        channels = 8
+        channels = 16
     L.b200ddp_set_sm_budget(148 - max(0, min(channels, 32)))
     return comm
 
