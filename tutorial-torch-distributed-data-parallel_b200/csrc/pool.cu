@@ -10,18 +10,40 @@ namespace b200 {
 
 constexpr int kPoolK = 3, kPoolS = 2;
 
+// Index walker for "flat index over [planes][rows][cols], advanced by a fixed step": one division at set-up, then
+// additions with carries (these kernels were instruction-bound on 64-bit divisions: ncu, issue slots 70 % busy).
+struct Walk3 {
+  int pl, r, c;            // current (plane, row, col)
+  int dpl, dr, dc;         // the step, decomposed
+  int rows, cols;
+  __device__ __forceinline__ Walk3(int start, int step, int rows_, int cols_) : rows(rows_), cols(cols_) {
+    const int per = rows_ * cols_;
+    pl = start / per; int t = start - pl * per; r = t / cols_; c = t - r * cols_;
+    dpl = step / per; t = step - dpl * per; dr = t / cols_; dc = t - dr * cols_;
+  }
+  __device__ __forceinline__ void next() {
+    c += dc;
+    const int k1 = c >= cols; c -= k1 ? cols : 0;
+    r += dr + k1;
+    const int k2 = r >= rows; r -= k2 ? rows : 0;
+    pl += dpl + k2;
+  }
+};
+
 // y[b,c,oh,ow] = max(0, max_{3x3 window} x); idx = window slot 0..8 of the first maximum, 255 when the
-// maximum is <= 0 (ReLU closed: no gradient flows).
+// maximum is <= 0 (ReLU closed: no gradient flows). One CTA per group of P whole planes, one thread per output.
 __global__ void __launch_bounds__(256) relu_maxpool_fwd_kernel(const float* __restrict__ x, float* __restrict__ y,
                                                                unsigned char* __restrict__ idx, long long planes,
-                                                               int H, int W, int OH, int OW, int relu) {
-  const long long total = planes * OH * OW, stride = (long long)gridDim.x * blockDim.x;
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
-    const int ow = (int)(i % OW);
-    const long long t = i / OW;
-    const int oh = (int)(t % OH);
-    const long long pl = t / OH;
-    const float* xp = x + pl * (long long)H * W + (long long)(oh * kPoolS) * W + ow * kPoolS;
+                                                               int H, int W, int OH, int OW, int relu, int P) {
+  const long long pl0 = (long long)blockIdx.x * P;
+  const int np = (int)(planes - pl0 < P ? planes - pl0 : P);
+  const int ohw = OH * OW, hw = H * W, n = np * ohw;
+  const float* xb = x + pl0 * hw;
+  float* yb = y + pl0 * ohw;
+  unsigned char* ib = idx + pl0 * ohw;
+  Walk3 wk(threadIdx.x, blockDim.x, OH, OW);
+  for (int i = threadIdx.x; i < n; i += blockDim.x, wk.next()) {
+    const float* xp = xb + wk.pl * hw + (wk.r * kPoolS) * W + wk.c * kPoolS;
     float best = -INFINITY;
     int bi = 0;
 #pragma unroll
@@ -36,8 +58,8 @@ __global__ void __launch_bounds__(256) relu_maxpool_fwd_kernel(const float* __re
       }
     unsigned char code = (unsigned char)bi;
     if (relu && !(best > 0.f)) { best = 0.f; code = 255; }
-    y[i] = best;
-    idx[i] = code;
+    yb[i] = best;
+    ib[i] = code;
   }
 }
 
@@ -75,7 +97,6 @@ __global__ void __launch_bounds__(256) relu_maxpool_bwd_kernel(const float* __re
   const long long planes = (long long)B * C;
   const long long nchunks = (planes + P - 1) / P;
   const int QH = (H + 1) >> 1, QW = (W + 1) >> 1, qhw = QH * QW;
-  const float inv_qhw = 1.0f / (float)qhw, inv_qw = 1.0f / (float)QW;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
   for (long long chunk = blockIdx.x; chunk < nchunks; chunk += gridDim.x) {
     const long long pl0 = chunk * P;
@@ -103,11 +124,9 @@ __global__ void __launch_bounds__(256) relu_maxpool_bwd_kernel(const float* __re
     // (a-1,b-1) the top-left pixel (slot 8): four (dy, slot) pairs from shared memory, nine compares, four stores.
     float* dxp = dx + pl0 * hw;
     const int n_quads = np * qhw;
-    for (int i = threadIdx.x; i < n_quads; i += blockDim.x) {
-      int pl = (int)(((float)i + 0.5f) * inv_qhw), rem = i - pl * qhw;      // exact: i < 2^23, see conv.cu
-      if (rem < 0) { --pl; rem += qhw; } else if (rem >= qhw) { ++pl; rem -= qhw; }
-      int a = (int)(((float)rem + 0.5f) * inv_qw), bq = rem - a * QW;
-      if (bq < 0) { --a; bq += QW; } else if (bq >= QW) { ++a; bq -= QW; }
+    Walk3 wk(threadIdx.x, blockDim.x, QH, QW);
+    for (int i = threadIdx.x; i < n_quads; i += blockDim.x, wk.next()) {
+      const int pl = wk.pl, a = wk.r, bq = wk.c;
       const float* sd = s_dy + pl * ohw;
       const unsigned char* si = s_idx + pl * ohw;
       const bool va = a < OH, vb = bq < OW, va0 = a > 0, vb0 = bq > 0;
@@ -226,7 +245,13 @@ int b200ddp_relu_maxpool_fwd(const float* x, float* y, unsigned char* idx, int B
   B200_DEVICE(device);
   const int OH = (H - kPoolK) / kPoolS + 1, OW = (W - kPoolK) / kPoolS + 1;
   const long long planes = (long long)B * C;
-  relu_maxpool_fwd_kernel<<<ew_grid(planes * OH * OW), 256, 0, as_stream(stream)>>>(x, y, idx, planes, H, W, OH, OW, relu);
+  B200_CHECK_ARG((long long)H * W < (1 << 24) , "relu_maxpool_fwd: plane too large");
+  int P = kPoolChunk / (OH * OW);
+  if (P < 1) P = 1;
+  while (P > 1 && (long long)P * H * W >= (1LL << 30)) --P;
+  const long long nblocks = (planes + P - 1) / P;
+  B200_CHECK_ARG(nblocks < (1LL << 31), "relu_maxpool_fwd: too many planes");
+  relu_maxpool_fwd_kernel<<<(unsigned)nblocks, 256, 0, as_stream(stream)>>>(x, y, idx, planes, H, W, OH, OW, relu, P);
   B200_LAUNCH_OK();
   return 0;
 }
