@@ -203,6 +203,47 @@ def conv_weight_matrix(w, mode: int):
     return out, ld
 
 
+# ---- side stream for weight gradients -------------------------------------------------------------------------------
+# dgrad and wgrad of a convolution depend only on the output gradient. dgrad is on the critical path of the backward
+# pass; at these sizes its grid is 169 or 338 tiles on 148 SMs, i.e. the last wave leaves most SMs idle. wgrad (one wave
+# of ~140 CTAs) is launched on a second stream so that the block scheduler fills those idle SMs with it. The main
+# stream re-joins before anything reads the weight gradients: the bucket all-reduce (reducer.py), optimizer.step and an
+# end-of-backward engine callback (so `.grad` is safe on the current stream when backward() returns).
+_SIDE = {}
+
+
+class _SideWork:
+    def __init__(self, device) -> None:
+        self.stream = torch.cuda.Stream(device)
+        self.pending = []
+        self.callback_queued = False
+
+
+def _side(device) -> "_SideWork":
+    key = (device.type, device.index)
+    w = _SIDE.get(key)
+    if w is None:
+        w = _SIDE[key] = _SideWork(device)
+    return w
+
+
+def join_side_work(device=None) -> None:
+    """Make the current stream wait for every weight-gradient kernel still running on the side stream."""
+    for key, w in _SIDE.items():
+        if device is not None and (device.type, device.index) != key:
+            continue
+        if w.pending:
+            cur = torch.cuda.current_stream(w.stream.device)
+            for ev in w.pending:
+                cur.wait_event(ev)
+            w.pending.clear()
+        w.callback_queued = False
+
+
+def _overlap_wgrad() -> bool:
+    return os.environ.get("B200DDP_WGRAD_SIDE_STREAM", "1") != "0"
+
+
 def _use_s2d(Cin: int, KH: int, KW: int, stride: int) -> bool:
     """Space-to-depth form of a strided convolution over few channels (the toy model's first layer)."""
     if os.environ.get("B200DDP_CONV1_S2D", "0") != "1":
@@ -341,9 +382,28 @@ class _Conv2dFn(torch.autograd.Function):
             ktab = _conv_tables(x.device, Cin, H, W, KH, KW) if ko == 0 else None
             nb = int(L.b200ddp_conv2d_wgrad_workspace_bytes(N, Cin, H, W, Cout, KH, KW, stride, pad))
             ws = _lib.workspace(x.device, max(nb, 256), "conv_wgrad")
+            wst = st
+            side = None
+            if ctx.needs_input_grad[0] and _overlap_wgrad():
+                # there is a dgrad to overlap with: run wgrad (+ its finalize) on the side stream
+                side = _side(x.device)
+                main = torch.cuda.current_stream(x.device)
+                ready = torch.cuda.Event()
+                ready.record(main)
+                side.stream.wait_event(ready)
+                for t in (x, dz):
+                    t.record_stream(side.stream)
+                wst = side.stream.cuda_stream
             _lib.check(L.b200ddp_conv2d_wgrad(x.data_ptr(), dz.data_ptr(), dw.data_ptr(), _lib.ptr(ktab), ko, N, Cin, H,
-                                              W, Cout, KH, KW, stride, pad, ws.data_ptr(), ws.numel(), dev, st),
+                                              W, Cout, KH, KW, stride, pad, ws.data_ptr(), ws.numel(), dev, wst),
                        "conv2d_wgrad")
+            if side is not None:
+                done = torch.cuda.Event()
+                done.record(side.stream)
+                side.pending.append(done)
+                if not side.callback_queued:
+                    side.callback_queued = True
+                    torch.autograd.Variable._execution_engine.queue_callback(lambda d=x.device: join_side_work(d))
         dx = None
         if ctx.needs_input_grad[0]:
             if stride != 1:

@@ -85,6 +85,8 @@ class Adam(Optimizer):
         if closure is not None:
             with torch.enable_grad():
                 loss = closure()
+        from .nn import join_side_work
+        join_side_work()
         for group in self.param_groups:
             params = [p for p in group["params"] if p.grad is not None]
             if not params:

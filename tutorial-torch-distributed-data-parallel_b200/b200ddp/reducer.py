@@ -179,6 +179,8 @@ class Reducer:
         t = self._bucket_tensor(b)
         n = b.end - b.start
         if self.cuda:
+            from .nn import join_side_work
+            join_side_work(t.device)       # weight gradients computed on the side stream must be complete
             L = _lib.load()
             dev, st = _lib.dev_index(t), _lib.cur_stream(t.device)
             if self.clip_value is not None:
