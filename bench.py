@@ -385,7 +385,7 @@ def run_b200(args) -> None:
     sync_all()
     launches = _lib.launch_count() - launches0
     ms = ev0.elapsed_time(ev1)
-    final_loss = float(loss)
+    final_loss = float(loss.detach())
     adam_ms = [a.elapsed_time(b) for a, b in adam_ev]
     t = torch.tensor([ms], dtype=torch.float64, device=dev)
     if world > 1:
