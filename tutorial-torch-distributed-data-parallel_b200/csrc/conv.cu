@@ -113,10 +113,13 @@ struct FwdShape {
 
 // TWO (only with BN == 64): the two-CTAs-per-SM shape, chosen by the host for short reduction loops (conv1 forward:
 // 18 k-blocks per tile); long loops (conv2 dgrad: 150) are faster with one CTA of three producer groups.
-template <int BN, int PL, bool TWO = false>
+// KS = 32-wide k-blocks per ring stage (1 or 2). With a 64-channel tile the four MMAs of a k-block take 128 cycles but
+// the MMA warp's barrier round (wait, fence, issue, commit) ~540: KS = 2 halves the rounds per reduction step.
+template <int BN, int PL, bool TWO = false, int KS = 1>
 __global__ void __launch_bounds__(FwdShape<TWO>::kThreads, FwdShape<TWO>::kCtasPerSm)
 conv_fwd_kernel(const __grid_constant__ CUtensorMap tmW, ConvFwdParams p) {
   static_assert(!TWO || BN == 64, "the two-CTA shape has room for a 64-column accumulator only");
+  static_assert(KS == 1 || KS == 2, "one or two k-blocks per stage");
   constexpr bool CI = PL >= 0;
   constexpr int kGroups = FwdShape<TWO>::kGroupsT, kProdWarps = FwdShape<TWO>::kProdWarpsT;
   extern __shared__ uint8_t smem_raw[];
@@ -126,9 +129,9 @@ conv_fwd_kernel(const __grid_constant__ CUtensorMap tmW, ConvFwdParams p) {
   // per k-block); with A in TMEM the STS and the MMA's A reads leave that pipe. Shared memory holds only the
   // TMA-fed weight tiles. TMEM: accumulator in columns [0, BN), A stage s in [kATmemCol0 + 32 s, +32).
   constexpr uint32_t B_BYTES = BN * CBK * 4;
-  constexpr uint32_t STAGE_BYTES = B_BYTES;
+  constexpr uint32_t STAGE_BYTES = KS * B_BYTES;
   constexpr uint32_t kATmemCol0 = FwdShape<TWO>::kATmemCol0T, kTmemCols = FwdShape<TWO>::kTmemColsT;
-  const int stages = p.stages;                        // <= FwdShape<TWO>::kMaxStages (32 A columns each)
+  const int stages = p.stages;                        // <= FwdShape<TWO>::kMaxStages / KS (32*KS A columns each)
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + (size_t)stages * STAGE_BYTES);
   uint64_t* empty_bar = full_bar + stages;
   uint64_t* tmem_full_bar = empty_bar + stages;
@@ -174,8 +177,8 @@ conv_fwd_kernel(const __grid_constant__ CUtensorMap tmW, ConvFwdParams p) {
     int cur_cblk = 0, cur_kh = 0, cur_kw = 0;  // CI: position of this group's next k-block to LOAD
     if (CI) {       // k-block kb = cblk * KH*KW + kh*KW + kw  (channel-block-major: the 32 channel planes of a
       const int khw = p.KH * p.KW;       // block are swept by all taps back to back, so they stay in L1)
-      cur_cblk = group / khw;
-      const int khkw = group - cur_cblk * khw;
+      cur_cblk = (group * KS) / khw;
+      const int khkw = group * KS - cur_cblk * khw;
       cur_kh = khkw / p.KW;
       cur_kw = khkw - cur_kh * p.KW;
     }
@@ -198,18 +201,19 @@ conv_fwd_kernel(const __grid_constant__ CUtensorMap tmW, ConvFwdParams p) {
 #else
 #define B200_TRACE(kb, slot)
 #endif
+    auto advance = [&](int steps) {           // move the (cblk, kh, kw) cursor forward by `steps` k-blocks
+      for (int t = 0; t < steps; ++t)
+        if (++cur_kw == p.KW) {
+          cur_kw = 0;
+          if (++cur_kh == p.KH) { cur_kh = 0; ++cur_cblk; }
+        }
+    };
     auto issue = [&](int kb, float (&v)[CBK]) {
       B200_TRACE(kb, 0);
       if (CI) {
         const bool ok = valid_m && (unsigned)(ih0 + cur_kh) < (unsigned)p.H && (unsigned)(iw0 + cur_kw) < (unsigned)p.W;
         const char* q = xb + (((long long)(cur_cblk << 5) * hw + cur_kh * p.W + cur_kw) << 2);
         load_strided<PL>(q, hw4, ok ? CBK : 0, v);     // constant stride H*W between channels
-#pragma unroll
-        for (int t = 0; t < kGroups; ++t)
-          if (++cur_kw == p.KW) {
-            cur_kw = 0;
-            if (++cur_kh == p.KH) { cur_kh = 0; ++cur_cblk; }
-          }
       } else {
         const int2* tab = p.tab + kb * CBK;
 #pragma unroll
@@ -221,36 +225,45 @@ conv_fwd_kernel(const __grid_constant__ CUtensorMap tmW, ConvFwdParams p) {
         }
       }
     };
-    int c_stage = group;                       // ring cursor of this group's next k-block to STORE (stages >= kGroups)
+    int c_stage = group;                       // ring cursor of this group's next stage to STORE (stages >= kGroups)
     uint32_t c_phase = 0;
-    auto commit = [&](int kb, const float (&v)[CBK]) {
+    auto commit = [&](int kb, int sub, const float (&v)[CBK]) {
       B200_TRACE(kb, 6);
-      mbar_wait(&empty_bar[c_stage], c_phase ^ 1u);
+      if (sub == 0) mbar_wait(&empty_bar[c_stage], c_phase ^ 1u);
       B200_TRACE(kb, 1);
       uint32_t rr[CBK];
 #pragma unroll
       for (int r = 0; r < CBK; ++r) rr[r] = __float_as_uint(round_tf32(v[r]));
-      tmem_st_32x32(t_lane + kATmemCol0 + (uint32_t)c_stage * CBK, rr);     // row = this thread's pixel, 32 K columns
-      tmem_wait_st();
-      B200_TRACE(kb, 7);
-      tc_fence_before();
-      mbar_arrive(&full_bar[c_stage]);
-      B200_TRACE(kb, 2);
-      c_stage += kGroups;
-      if (c_stage >= stages) { c_stage -= stages; c_phase ^= 1u; }
+      // row = this thread's pixel, 32 K columns of sub-block `sub` of the stage
+      tmem_st_32x32(t_lane + kATmemCol0 + (uint32_t)(c_stage * KS + sub) * CBK, rr);
+      if (sub == KS - 1) {
+        tmem_wait_st();
+        B200_TRACE(kb, 7);
+        tc_fence_before();
+        mbar_arrive(&full_bar[c_stage]);
+        B200_TRACE(kb, 2);
+        c_stage += kGroups;
+        if (c_stage >= stages) { c_stage -= stages; c_phase ^= 1u; }
+      }
     };
     {
+      // this group's items, in order: stage j = group, group + G, ...; within a stage the sub-blocks 0..KS-1;
+      // item i is k-block (group + (i / KS) * G) * KS + i % KS. Loads of item i+1 are in flight while item i is stored.
+      const int nstage = p.kblocks / KS;                      // host guarantees kblocks % KS == 0
+      const int my_stages = group < nstage ? (nstage - group + kGroups - 1) / kGroups : 0;
+      const int nitems = my_stages * KS;
+      auto kb_of = [&](int i) { return (group + (i / KS) * kGroups) * KS + (i % KS); };
+      auto step_after = [&](int i) { return (i % KS) == KS - 1 ? kGroups * KS - (KS - 1) : 1; };
       float va[CBK], vb[CBK];
-      int kb = group;
-      if (kb < p.kblocks) issue(kb, va);
-      while (kb < p.kblocks) {
-        const int kb2 = kb + kGroups;
-        if (kb2 < p.kblocks) issue(kb2, vb);
-        commit(kb, va);
-        if (kb2 >= p.kblocks) break;
-        kb = kb2 + kGroups;
-        if (kb < p.kblocks) issue(kb, va);
-        commit(kb2, vb);
+      int i = 0;
+      if (nitems > 0) { issue(kb_of(0), va); if (CI) advance(step_after(0)); }
+      while (i < nitems) {
+        if (i + 1 < nitems) { issue(kb_of(i + 1), vb); if (CI) advance(step_after(i + 1)); }
+        commit(kb_of(i), i % KS, va);
+        if (++i >= nitems) break;
+        if (i + 1 < nitems) { issue(kb_of(i + 1), va); if (CI) advance(step_after(i + 1)); }
+        commit(kb_of(i), i % KS, vb);
+        ++i;
       }
     }
     // ---------------- epilogue: TMEM lane = pixel, columns = output channels; 32-column chunks round-robin over groups ----------------
@@ -277,18 +290,20 @@ conv_fwd_kernel(const __grid_constant__ CUtensorMap tmW, ConvFwdParams p) {
   } else if (warp == kProdWarps) {
     // ---------------- MMA issuer ----------------
     const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(CBM >> 4) << 24);
-    mma_issue_loop_ts<CBK / CUK>(tmem_base, tmem_base + kATmemCol0, CBK, idesc, smem_u32(smem), STAGE_BYTES,
-                                 operand_k_major(), smem_u32(&full_bar[0]), smem_u32(&empty_bar[0]),
-                                 smem_u32(tmem_full_bar), stages, p.kblocks);
+    mma_issue_loop_ts<CBK / CUK, KS>(tmem_base, tmem_base + kATmemCol0, CBK * KS, idesc, smem_u32(smem), STAGE_BYTES,
+                                     operand_k_major(), smem_u32(&full_bar[0]), smem_u32(&empty_bar[0]),
+                                     smem_u32(tmem_full_bar), stages, p.kblocks / KS, B_BYTES);
   } else if (lane == 0) {
     // ---------------- weight-tile TMA producer: runs the whole ring ahead of the gather groups, so the B tile of
     // a stage is requested the moment the stage frees up instead of when a gather group gets round to it ----------------
     int s = 0;
     uint32_t ph = 0;
-    for (int kb = 0; kb < p.kblocks; ++kb) {
+    for (int kb = 0; kb < p.kblocks; kb += KS) {
       mbar_wait(&empty_bar[s], ph ^ 1u);
-      mbar_arrive_expect_tx(&full_bar[s], B_BYTES);
-      tma_load_2d(smem + (size_t)s * STAGE_BYTES, &tmW, &full_bar[s], kb * CBK, n0);    // box {32 k, BN co}
+      mbar_arrive_expect_tx(&full_bar[s], STAGE_BYTES);
+#pragma unroll
+      for (int sub = 0; sub < KS; ++sub)      // box {32 k, BN co} each
+        tma_load_2d(smem + (size_t)s * STAGE_BYTES + sub * B_BYTES, &tmW, &full_bar[s], (kb + sub) * CBK, n0);
       if (++s == stages) { s = 0; ph ^= 1u; }
     }
   }
@@ -700,13 +715,13 @@ inline int cs_splits(int Nb, int C) {
   return s < 1 ? 1 : s;
 }
 
-template <int BN, int PL, bool TWO = false>
+template <int BN, int PL, bool TWO = false, int KS = 1>
 int launch_fwd(const CUtensorMap& tmW, const ConvFwdParams& p, cudaStream_t stream) {
-  const size_t stage_bytes = (size_t)BN * CBK * 4;       // weight tile only: the im2col tile lives in TMEM
+  const size_t stage_bytes = (size_t)BN * CBK * 4 * KS;  // weight tiles only: the im2col tile lives in TMEM
   const size_t smem = 1024 + (size_t)p.stages * stage_bytes + (2 * p.stages + 1) * 8 + 16;
   static bool attr_set = false;
   if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(conv_fwd_kernel<BN, PL, TWO>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    cudaError_t e = cudaFuncSetAttribute(conv_fwd_kernel<BN, PL, TWO, KS>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
     if (e != cudaSuccess) {
       set_error("cudaFuncSetAttribute(conv_fwd_kernel<%d>) -> %s", BN, cudaGetErrorString(e));
       return kCudaErrBase + (int)e;
@@ -714,7 +729,7 @@ int launch_fwd(const CUtensorMap& tmW, const ConvFwdParams& p, cudaStream_t stre
     attr_set = true;
   }
   dim3 grid((p.M + CBM - 1) / CBM, (p.Cout + BN - 1) / BN, 1);
-  conv_fwd_kernel<BN, PL, TWO><<<grid, FwdShape<TWO>::kThreads, smem, stream>>>(tmW, p);
+  conv_fwd_kernel<BN, PL, TWO, KS><<<grid, FwdShape<TWO>::kThreads, smem, stream>>>(tmW, p);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) {
     set_error("conv_fwd_kernel<%d> launch (grid %d,%d smem %zu) -> %s", BN, grid.x, grid.y, smem, cudaGetErrorString(e));
@@ -828,10 +843,12 @@ int b200ddp_conv2d_fwd(const float* x, const float* wmat, long long ldw, const f
   // which leaves >= ~90 KB of the SM array as L1 for the channel-block-major reuse
   int stages = (int)((160 * 1024) / ((size_t)bn * CBK * 4));
   const bool two = bn == 64 && p.kblocks <= 32;      // short tiles: two CTAs per SM
-  const int max_stages = two ? FwdShape<true>::kMaxStages : FwdShape<false>::kMaxStages;
+  // 64-channel tiles with a long, even reduction (conv2 dgrad): two k-blocks per stage
+  const int ks = (!two && bn == 64 && k_order == 1 && p.kblocks >= 16 && p.kblocks % 2 == 0) ? 2 : 1;
+  const int max_stages = (two ? FwdShape<true>::kMaxStages : FwdShape<false>::kMaxStages) / ks;
   const int groups = two ? FwdShape<true>::kGroupsT : FwdShape<false>::kGroupsT;
   if (stages > max_stages) stages = max_stages;
-  if (stages > p.kblocks) stages = p.kblocks;
+  if (stages > p.kblocks / ks) stages = p.kblocks / ks;
   if (stages < groups) stages = groups;
   p.stages = stages;
   CUtensorMap tmW;
@@ -850,6 +867,10 @@ int b200ddp_conv2d_fwd(const float* x, const float* wmat, long long ldw, const f
     if (two) {                                                         // conv1 after space-to-depth, small test shapes
       if (plane == 57 * 57) return launch_fwd<64, 57 * 57, true>(tmW, p, s);
       return launch_fwd<64, 0, true>(tmW, p, s);
+    }
+    if (ks == 2) {                                                     // bn == 64
+      if (plane == 27 * 27) return launch_fwd<64, 27 * 27, false, 2>(tmW, p, s);
+      return launch_fwd<64, 0, false, 2>(tmW, p, s);
     }
     if (plane == 27 * 27) { B200_FWD_BN(27 * 27) }
     if (plane == 13 * 13) { B200_FWD_BN(13 * 13) }

@@ -261,11 +261,12 @@ __device__ __forceinline__ void umma_tf32_ts(uint32_t tmem_d, uint32_t tmem_a, u
 
 // MMA loop for the TS form: A stage s = TMEM columns [tmem_a0 + s*a_stage_cols, +UMMAS*8), B stage s in shared
 // memory at smem_saddr + s*stage_bytes. Same warp-uniform structure as mma_issue_loop.
-template <int UMMAS>
+// KSUB k-blocks per stage: their A columns are contiguous (32 each), their B tiles b_sub_bytes apart.
+template <int UMMAS, int KSUB = 1>
 __device__ __forceinline__ void mma_issue_loop_ts(uint32_t tmem_d, uint32_t tmem_a0, uint32_t a_stage_cols, uint32_t idesc,
                                                   uint32_t smem_saddr, uint32_t stage_bytes, OperandDesc b,
                                                   uint32_t full_saddr, uint32_t empty_saddr, uint32_t tmem_full_saddr,
-                                                  int stages, int nkb) {
+                                                  int stages, int nkb, uint32_t b_sub_bytes = 0) {
   const uint32_t b_lo0 = ((smem_saddr & 0x3FFFFu) >> 4) | ((b.lbo >> 4) << 16);
   const uint32_t b_hi = (b.sbo >> 4) | (1u << 14) | (b.layout_type << 29);
   const uint32_t b_step = b.k_advance >> 4, stage_step = stage_bytes >> 4;
@@ -277,7 +278,11 @@ __device__ __forceinline__ void mma_issue_loop_ts(uint32_t tmem_d, uint32_t tmem
     tc_fence_after();
     if (elect_one()) {
 #pragma unroll
-      for (int k = 0; k < UMMAS; ++k) umma_tf32_ts(tmem_d, ta + k * 8u, b_lo + k * b_step, b_hi, idesc, k ? 1u : acc);
+      for (int sub = 0; sub < KSUB; ++sub)
+#pragma unroll
+        for (int k = 0; k < UMMAS; ++k)
+          umma_tf32_ts(tmem_d, ta + (uint32_t)(sub * UMMAS + k) * 8u, b_lo + sub * (b_sub_bytes >> 4) + k * b_step, b_hi, idesc,
+                       (sub | k) ? 1u : acc);
       umma_commit_addr(eb);               // frees the TMEM A stage and the smem B stage when these MMAs retire
     }
     acc = 1u;
