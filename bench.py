@@ -42,7 +42,7 @@ P_PARAMS = 57_044_810
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=30)
+    ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--mode", default="tf32", choices=["tf32", "fp32"])
@@ -54,8 +54,8 @@ def parse():
 
 # ---- clocks ---------------------------------------------------------------------------------------------------
 class ClockSampler:
-    """SM clock + throttle reasons sampled DURING the timed regions: NVML polled every 5 ms from a thread
-    (a 30-step region lasts ~0.1 s), nvidia-smi -lms 20 as the fallback when pynvml cannot open the device."""
+    """SM clock + throttle reasons sampled DURING the timed regions: NVML polled every 25 ms from a thread
+    (a 200-step region lasts ~0.5 s), nvidia-smi -lms 20 as the fallback when pynvml cannot open the device."""
     REASONS = (("hw_slowdown", 0x8), ("hw_thermal_slowdown", 0x40), ("sw_thermal_slowdown", 0x20), ("sw_power_cap", 0x4))
     QUERY = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
              "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
@@ -70,6 +70,9 @@ class ClockSampler:
         self.stop_flag = threading.Event()
         self.thread = None
         self.source = None
+        # polling period: NVML queries take driver locks that kernel launches also need; 5 ms polling produced
+        # occasional 10-20 ms launch stalls in a 50 ms timed region, 25 ms does not
+        self.interval = float(os.environ.get("B200DDP_BENCH_CLOCK_MS", "25")) / 1e3
 
     def _nvml_handle(self):
         import pynvml
@@ -94,15 +97,18 @@ class ClockSampler:
                 self.samples.append((float(mhz), int(mask)))
             except Exception:
                 pass
-            time.sleep(0.005)
+            time.sleep(self.interval)
 
     def start(self) -> None:
+        if self.interval <= 0:
+            self.source = None
+            return
         try:
             pynvml, h = self._nvml_handle()
             self.max_mhz = float(pynvml.nvmlDeviceGetMaxClockInfo(h, pynvml.NVML_CLOCK_SM))
             self.thread = threading.Thread(target=self._poll, args=(pynvml, h), daemon=True)
             self.thread.start()
-            self.source = "nvml 5 ms"
+            self.source = f"nvml {self.interval * 1e3:.0f} ms"
             return
         except Exception:
             self.thread = None
@@ -365,6 +371,9 @@ def run_b200(args) -> None:
     if rank == 0:
         clocks.start()
         time.sleep(0.02)
+    import gc
+    gc.collect()
+    gc.disable()          # a collector pause inside a 0.1-0.5 s timed region is a multi-ms launch stall
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     adam_ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
     launches0 = _lib.launch_count()
@@ -446,6 +455,7 @@ def run_b200(args) -> None:
     h2d = B * 3 * 224 * 224 * 4 + B * 8
     d2h = 4
 
+    gc.enable()
     # ---- per-kernel CUDA-event timing of the same step (device-resident inputs), for the roofline of the dominant kernel ----
     clock_info = clocks.stop() if rank == 0 else None      # covers both timed regions (resident and end to end)
     _lib.enable_timing()

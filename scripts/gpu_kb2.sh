@@ -1,6 +1,6 @@
 #!/bin/bash
 mkdir -p gpurun_out
-timeout 600 python scripts/kernel_bench.py --only "conv2d_dgrad conv2" > gpurun_out/kb_dgrad.log 2>&1; echo "rc=$?"
+timeout 600 python scripts/kernel_bench.py --only "conv2d_dgrad conv" > gpurun_out/kb_dgrad.log 2>&1; echo "rc=$?"
 timeout 600 python scripts/kernel_bench.py --only "conv2d_fwd conv" >> gpurun_out/kb_dgrad.log 2>&1; echo "rc=$?"
 python - <<'PY'
 import json

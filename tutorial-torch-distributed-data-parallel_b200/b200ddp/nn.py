@@ -375,6 +375,18 @@ class _Conv2dFn(torch.autograd.Function):
             scratch = _lib.workspace(x.device, nb, "chsum", zero=True)
             _lib.check(L.b200ddp_channel_sum(dz.data_ptr(), db.data_ptr(), N, Cout, OH * OW, scratch.data_ptr(),
                                              scratch.numel(), dev, st), "channel_sum")
+        # dgrad first: it is on the critical path and should own the SMs' first wave; wgrad then fills its tail
+        dx = None
+        if ctx.needs_input_grad[0]:
+            if stride != 1:
+                raise NotImplementedError("b200ddp Conv2d: input gradients are implemented for stride 1 only "
+                                          "(the toy model's strided conv is its first layer)")
+            ko = _k_order(Cout)          # dgrad reduces over (co, kh', kw')
+            if ctx.dgrad_weights is not None:
+                wt, ldt = ctx.dgrad_weights
+            else:
+                wt, ldt = conv_weight_matrix(w, 3 if ko == 1 else 1)
+            dx = conv2d_forward_raw(dz, wt, ldt, None, Cin, KH, KW, 1, KH - 1 - pad, False, ko)
         dw = None
         if ctx.needs_input_grad[1]:
             dw = _grad_target(ctx.weight_param, tuple(w.shape), x.device)
@@ -404,17 +416,6 @@ class _Conv2dFn(torch.autograd.Function):
                 if not side.callback_queued:
                     side.callback_queued = True
                     torch.autograd.Variable._execution_engine.queue_callback(lambda d=x.device: join_side_work(d))
-        dx = None
-        if ctx.needs_input_grad[0]:
-            if stride != 1:
-                raise NotImplementedError("b200ddp Conv2d: input gradients are implemented for stride 1 only "
-                                          "(the toy model's strided conv is its first layer)")
-            ko = _k_order(Cout)          # dgrad reduces over (co, kh', kw')
-            if ctx.dgrad_weights is not None:
-                wt, ldt = ctx.dgrad_weights
-            else:
-                wt, ldt = conv_weight_matrix(w, 3 if ko == 1 else 1)
-            dx = conv2d_forward_raw(dz, wt, ldt, None, Cin, KH, KW, 1, KH - 1 - pad, False, ko)
         return dx, dw, db, None, None, None, None, None
 
 

@@ -841,12 +841,13 @@ int b200ddp_conv2d_fwd(const float* x, const float* wmat, long long ldw, const f
   const int bn = pick_bn(Cout);
   // ring depth: 8 A stages fit the TMEM columns left of the accumulator; the weight-tile ring is <= 8 x 32 KB,
   // which leaves >= ~90 KB of the SM array as L1 for the channel-block-major reuse
-  int stages = (int)((160 * 1024) / ((size_t)bn * CBK * 4));
+  int stages = (int)((160 * 1024) / ((size_t)bn * CBK * 4));      // refined below once KS is known
   const bool two = bn == 64 && p.kblocks <= 32;      // short tiles: two CTAs per SM
   // 64-channel tiles with a long, even reduction (conv2 dgrad): two k-blocks per stage
-  const int ks = (!two && bn == 64 && k_order == 1 && p.kblocks >= 16 && p.kblocks % 2 == 0) ? 2 : 1;
+  const int ks = (!two && bn <= 192 && k_order == 1 && p.kblocks >= 16 && p.kblocks % 2 == 0) ? 2 : 1;
   const int max_stages = (two ? FwdShape<true>::kMaxStages : FwdShape<false>::kMaxStages) / ks;
   const int groups = two ? FwdShape<true>::kGroupsT : FwdShape<false>::kGroupsT;
+  stages /= ks;
   if (stages > max_stages) stages = max_stages;
   if (stages > p.kblocks / ks) stages = p.kblocks / ks;
   if (stages < groups) stages = groups;
@@ -868,9 +869,17 @@ int b200ddp_conv2d_fwd(const float* x, const float* wmat, long long ldw, const f
       if (plane == 57 * 57) return launch_fwd<64, 57 * 57, true>(tmW, p, s);
       return launch_fwd<64, 0, true>(tmW, p, s);
     }
-    if (ks == 2) {                                                     // bn == 64
-      if (plane == 27 * 27) return launch_fwd<64, 27 * 27, false, 2>(tmW, p, s);
-      return launch_fwd<64, 0, false, 2>(tmW, p, s);
+    if (ks == 2) {                                                     // bn <= 192
+#define B200_FWD_KS2(PLV)                                                       \
+      switch (bn) {                                                             \
+        case 64: return launch_fwd<64, PLV, false, 2>(tmW, p, s);               \
+        case 128: return launch_fwd<128, PLV, false, 2>(tmW, p, s);             \
+        default: return launch_fwd<192, PLV, false, 2>(tmW, p, s);              \
+      }
+      if (plane == 27 * 27) { B200_FWD_KS2(27 * 27) }
+      if (plane == 13 * 13) { B200_FWD_KS2(13 * 13) }
+      B200_FWD_KS2(0)
+#undef B200_FWD_KS2
     }
     if (plane == 27 * 27) { B200_FWD_BN(27 * 27) }
     if (plane == 13 * 13) { B200_FWD_BN(13 * 13) }
