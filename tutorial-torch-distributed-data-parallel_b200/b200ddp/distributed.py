@@ -128,7 +128,31 @@ class DistributedDataParallel(nn.Module):
                     self._broadcast_buffers()
         elif torch.is_grad_enabled():
             self.reducer.require_sync = False
-        return self.module(*inputs, **kwargs)
+        out = self.module(*inputs, **kwargs)
+        self.reducer.pass_prescaled = False
+        if (self.reducer.prescale and torch.is_grad_enabled() and self.require_backward_grad_sync
+                and self.world_size > 1):
+            # Mean over ranks = plain SUM of gradients that are already divided by the world size: scaling the
+            # gradient that enters the model (one tiny multiply) lets the all-reduce use ncclSum, which NCCL can run
+            # as an in-switch NVLS reduction on NVSwitch systems (user-defined PreMulSum falls back to RING).
+            inv = 1.0 / self.world_size
+            scaled = [False]
+
+            def _scale(t):
+                if torch.is_tensor(t) and t.requires_grad:
+                    t.register_hook(lambda g: g * inv)
+                    scaled[0] = True
+                return t
+            if torch.is_tensor(out):
+                _scale(out)
+            elif isinstance(out, (tuple, list)):
+                for t in out:
+                    _scale(t)
+            elif isinstance(out, dict):
+                for t in out.values():
+                    _scale(t)
+            self.reducer.pass_prescaled = scaled[0]
+        return out
 
     @contextmanager
     def no_sync(self):
@@ -136,6 +160,7 @@ class DistributedDataParallel(nn.Module):
         old = self.require_backward_grad_sync
         self.require_backward_grad_sync = False
         self.reducer.require_sync = False
+        self.reducer.prescale = False      # locally accumulated gradients are unscaled: keep PreMulSum from here on
         try:
             yield
         finally:
