@@ -4,29 +4,33 @@
 // (The reference runs these through cuDNN, also in TF32 — torch's default for convolutions.)
 //
 // No im2col matrix is ever materialised and no NCHW<->NHWC conversion pass runs (the stock path spends
-// ~1 ms per step in cudnn::nchwToNhwcKernel / nhwcToNchwKernel): producer warps gather the im2col tile of
-// each k-block directly into shared memory in the swizzled layout tcgen05.mma expects, the weight tile
-// arrives by TMA, one thread issues the MMAs, and the producer warps then run the epilogue.
+// ~1 ms per step in cudnn::nchwToNhwcKernel / nhwcToNchwKernel).
 //
-//   forward / dgrad   D[m = pixel][n = co] = sum_k  col(pixel, k) * W[co][k]
-//       A = col tile, MN-major (32 consecutive output pixels are contiguous in smem and — for stride 1 —
-//           in the input row), layout SWIZZLE_128B_BASE32B; B = W rows, K-major, TMA SWIZZLE_128B.
-//       Epilogue: + bias[co], ReLU, coalesced stores y[n][co][pix] (lanes = consecutive pixels).
+//   forward / dgrad   D[m = pixel][n = co] = sum_k  col(pixel, k) * W[co][k]          (conv_fwd_kernel)
+//       A = im2col tile: producer warps gather it (thread <-> output pixel, 32 k values in registers), round to
+//           TF32 and write their tile row into TENSOR MEMORY with one tcgen05.st; the MMA is the TS form
+//           tcgen05.mma [d_tmem], [a_tmem], b_desc. B = W rows, K-major, TMA SWIZZLE_128B into a shared-memory
+//           ring filled by a dedicated TMA warp. One warp issues the MMAs (warp-uniform loop, elect.sync).
+//       Epilogue (the producer warps): tcgen05.ld, + bias[co], ReLU, coalesced stores y[n][co][pix].
 //       dgrad of a stride-1 convolution is the same kernel run on dY with the flipped / transposed
 //       weights produced by conv_weight_prep (pad' = KH-1-pad).
-//   wgrad             D[m = k][n = co]     = sum_pixel col(pixel, k) * dY[co][pixel]
-//       both operands K-major (32 consecutive pixels per smem row), gathered by the producer warps;
-//       the pixel range is split over CTAs (deterministic partials + finalize) because only
-//       ceil(K/128) x ceil(Cout/BN) output tiles exist.
+//   wgrad             D[m = k][n = co]     = sum_pixel col(pixel, k) * dY[co][pixel]   (conv_wgrad_kernel)
+//       both operands K-major (32 consecutive pixels per smem row, SWIZZLE_128B), gathered by the producer
+//       warps into shared memory (the TMEM form would need lane = k-row, i.e. uncoalesced loads); R row
+//       sub-tiles per CTA share one gathered dY tile (R accumulators in TMEM); the pixel range is split over
+//       CTAs (deterministic partials + finalize) because only ceil(K/(128 R)) x ceil(Cout/BN) tiles exist.
 //
 // Two orderings of the reduction index k (the weight matrix is permuted to match by conv_weight_prep):
-//   k_order 0  k = (ci, kh, kw)   torch's own order; per-k offsets come from a small device table. Any Cin.
-//   k_order 1  k = (ci/32, kh, kw, ci%32)   "channel-block-major", needs Cin % 32 == 0: a whole 32-row k-block shares one
-//              (kh, kw), so each producer thread does ONE bounds test per k-block and walks the channels
-//              with a constant stride of H*W — ~6 instructions per gathered element instead of ~20.
+//   k_order 0  k = (ci, kh, kw)   torch's own order; per-k offsets + window bits come from a device table. Any Cin.
+//   k_order 1  k = (ci/32, kh, kw, ci%32)   "channel-block-major", needs Cin % 32 == 0: a whole 32-row k-block
+//              shares one (kh, kw) - one bounds test per k-block, loads `base + r * plane` with the plane size a
+//              template constant for the toy model's shapes - and the 32-channel slab of the tile's rows is
+//              re-read by every tap, so it stays in L1.
 //
-// Producers: kGroups groups of 4 warps; group g fills k-blocks g, g+kGroups, ... with 32 independent
-// loads in flight per thread, rounds to TF32 (round-half-up on the magnitude: one integer add) and stores.
+// What bounds these kernels, as measured (profiles/r01_summary.md): the MMA-issuing warp's barrier round, then
+// the instruction count of the gather, then the unified L1/shared-memory data pipe (hence A in TMEM), then the
+// bytes gathered per MMA (hence R sub-tiles in wgrad), then the per-tile fixed cost for short reductions
+// (hence the two-CTAs-per-SM shape for conv1).
 #include "gemm.h"
 #include "tc.cuh"
 #include "../../include/b200ddp.h"
@@ -838,7 +842,7 @@ int b200ddp_conv2d_fwd(const float* x, const float* wmat, long long ldw, const f
 #ifdef B200_CONV_TRACE
   p.trace = g_conv_trace;
 #endif
-  const int bn = pick_bn(Cout);
+  const int bn = pick_bn(Cout);     // (128-wide tiles for the 256-channel layers were measured: 99 vs 95 us, no)
   // ring depth: 8 A stages fit the TMEM columns left of the accumulator; the weight-tile ring is <= 8 x 32 KB,
   // which leaves >= ~90 KB of the SM array as L1 for the channel-block-major reuse
   int stages = (int)((160 * 1024) / ((size_t)bn * CBK * 4));      // refined below once KS is known
