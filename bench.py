@@ -458,11 +458,19 @@ def run_b200(args) -> None:
     gc.enable()
     # ---- per-kernel CUDA-event timing of the same step (device-resident inputs), for the roofline of the dominant kernel ----
     clock_info = clocks.stop() if rank == 0 else None      # covers both timed regions (resident and end to end)
+    # (the side stream that overlaps weight-gradient kernels with dgrad is switched off for this pass: an event pair
+    # around a kernel that shares the SMs with another stream's kernel measures the interference, not the kernel)
+    prev_side = os.environ.get("B200DDP_WGRAD_SIDE_STREAM")
+    os.environ["B200DDP_WGRAD_SIDE_STREAM"] = "0"
     _lib.enable_timing()
     n_prof = min(args.steps, 10)
     for k in range(n_prof):
         step_resident(k)
     calls = _lib.disable_timing()
+    if prev_side is None:
+        del os.environ["B200DDP_WGRAD_SIDE_STREAM"]
+    else:
+        os.environ["B200DDP_WGRAD_SIDE_STREAM"] = prev_side
     kernels = summarize_kernels(calls, n_prof)
 
     if rank == 0:
