@@ -549,15 +549,32 @@ conv_wgrad_kernel(ConvWgradParams p) {
 // dW[co][ci][kh][kw] = sum_z ws[z][co][((ci/32)*KH*KW + kh*KW + kw)*32 + ci%32]   (k_order 1 partials -> torch order)
 __global__ void __launch_bounds__(256) wgrad_finalize_ci_kernel(const float* __restrict__ ws, int splits, int Cout, int Cin,
                                                                 int KHW, float* __restrict__ dw) {
-  const long long K = (long long)Cin * KHW, total = (long long)Cout * K, stride = (long long)gridDim.x * blockDim.x;
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
-    // i enumerates the GEMM order (coalesced reads): co, (cblk, khkw, ci % 32)
-    const long long co = i / K, k = i - co * K;
-    const int slab = (int)(k >> 5), cblk = slab / KHW, khkw = slab - cblk * KHW;
-    const int ci = (cblk << 5) + (int)(k & 31);
-    float s = 0.f;
-    for (int z = 0; z < splits; ++z) s += __ldg(ws + (long long)z * total + i);
-    dw[co * K + (long long)ci * KHW + khkw] = s;
+  // one thread per 4 consecutive GEMM-order k of one output channel (K % 32 == 0: the four share (cblk, khkw) and are
+  // four consecutive channels): 16-byte loads of the partials, four slices in flight, 32-bit index arithmetic.
+  // Partials are added in slice order (deterministic).
+  const int K = Cin * KHW, K4 = K >> 2;
+  const int total4 = Cout * K4;                       // host guarantees Cout*K < 2^31
+  const long long slice4 = ((long long)Cout * K) >> 2;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total4; i += gridDim.x * blockDim.x) {
+    const int co = i / K4, k = (i - co * K4) << 2;
+    const float4* src = reinterpret_cast<const float4*>(ws) + i;
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+    int z = 0;
+    for (; z + 4 <= splits; z += 4) {
+      float4 v[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) v[u] = __ldg(src + (long long)(z + u) * slice4);
+#pragma unroll
+      for (int u = 0; u < 4; ++u) { acc.x += v[u].x; acc.y += v[u].y; acc.z += v[u].z; acc.w += v[u].w; }
+    }
+    for (; z < splits; ++z) {
+      const float4 v = __ldg(src + (long long)z * slice4);
+      acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+    }
+    const int slab = k >> 5, cblk = slab / KHW, khkw = slab - cblk * KHW;
+    const int ci = (cblk << 5) + (k & 31);
+    float* o = dw + (long long)co * K + (long long)ci * KHW + khkw;      // torch order: channels KHW apart
+    o[0] = acc.x; o[KHW] = acc.y; o[2 * KHW] = acc.z; o[3 * KHW] = acc.w;
   }
 }
 
@@ -592,33 +609,38 @@ __device__ __forceinline__ void weight_prep_body(const float* __restrict__ w, fl
   }
   if (mode == 0) {
     const int K = Cin * KHW;
-    const long long total = (long long)Cout * ld_out;
-    for (long long i = first; i < total; i += stride) {
-      const int co = (int)(i / ld_out), k = (int)(i - (long long)co * ld_out);
+    const int total = Cout * (int)ld_out, ld = (int)ld_out;       // host guarantees < 2^31
+    for (int i = (int)first; i < total; i += (int)stride) {
+      const int co = i / ld, k = i - co * ld;
       out[i] = k < K ? __ldg(w + (long long)co * K + k) : 0.f;
     }
   } else if (mode == 2 || mode == 3) {
-    const long long total = (long long)Cout * Cin * KHW;
-    for (long long i = first; i < total; i += stride) {
-      // i enumerates the INPUT w[co][ci][kh][kw]
-      const int kw = (int)(i % KW);
-      long long t = i / KW;
-      const int kh = (int)(t % KH);
-      t /= KH;
-      const int ci = (int)(t % Cin), co = (int)(t / Cin);
-      const float v = __ldg(w + i);
-      if (mode == 2) out[(long long)co * ld_out + ((long long)(ci >> 5) * KHW + kh * KW + kw) * 32 + (ci & 31)] = v;
-      else out[(long long)ci * ld_out + ((long long)(co >> 5) * KHW + (KH - 1 - kh) * KW + (KW - 1 - kw)) * 32 + (co & 31)] = v;
+    // i enumerates the OUTPUT (coalesced stores; the strided reads of the 10 MB of weights are served by L2)
+    const int total = Cout * Cin * KHW;                           // host guarantees < 2^31
+    if (mode == 2) {
+      const int K = Cin * KHW;
+      for (int i = (int)first; i < total; i += (int)stride) {
+        const int co = i / K, k = i - co * K;
+        const int slab = k >> 5, cblk = slab / KHW, khkw = slab - cblk * KHW, ci = (cblk << 5) + (k & 31);
+        out[(long long)co * ld_out + k] = __ldg(w + ((long long)co * Cin + ci) * KHW + khkw);
+      }
+    } else {
+      const int Kp = Cout * KHW;
+      for (int i = (int)first; i < total; i += (int)stride) {
+        const int ci = i / Kp, k = i - ci * Kp;
+        const int slab = k >> 5, cob = slab / KHW, khkwp = slab - cob * KHW, co = (cob << 5) + (k & 31);
+        out[(long long)ci * ld_out + k] = __ldg(w + ((long long)co * Cin + ci) * KHW + (KHW - 1 - khkwp));
+      }
     }
   } else {
-    const long long total = (long long)Cout * Cin * KHW;
-    for (long long i = first; i < total; i += stride) {
+    const int total = Cout * Cin * KHW;
+    for (int i = (int)first; i < total; i += (int)stride) {
       // i enumerates the OUTPUT: [ci][co][kh'][kw']
-      const int kwp = (int)(i % KW);
-      long long t = i / KW;
-      const int khp = (int)(t % KH);
+      const int kwp = i % KW;
+      int t = i / KW;
+      const int khp = t % KH;
       t /= KH;
-      const int co = (int)(t % Cout), ci = (int)(t / Cout);
+      const int co = t % Cout, ci = t / Cout;
       const long long src = (((long long)co * Cin + ci) * KH + (KH - 1 - khp)) * KW + (KW - 1 - kwp);
       out[(long long)ci * ld_out + (long long)co * KHW + khp * KW + kwp] = __ldg(w + src);
     }
@@ -958,8 +980,9 @@ int b200ddp_conv2d_wgrad(const float* x, const float* dy, float* dw, const int* 
   if (w.splits > 1) {
     if (k_order == 1) {
       const long long total = (long long)Cout * K;
-      long long want = (total + 255) / 256;
-      const int grid = (int)(want < kNumSMs * 8 ? want : kNumSMs * 8);
+      B200_CHECK_ARG(total < (1LL << 31), "conv2d_wgrad: weight tensor too large");
+      long long want = (total / 4 + 255) / 256;
+      const int grid = (int)(want < kNumSMs * 16 ? want : kNumSMs * 16);
       wgrad_finalize_ci_kernel<<<grid, 256, 0, s>>>(reinterpret_cast<const float*>(ws), w.splits, Cout, Cin, KH * KW, dw);
       B200_LAUNCH_OK();
       return 0;
@@ -982,6 +1005,12 @@ static int check_prep_mode(int Cout, int Cin, int KH, int KW, long long ld_out, 
                  "%s: ld_out too small", who);
   return 0;
 }
+static long long prep_total(int Cout, int Cin, int KH, int KW, long long ld_out, int mode);
+static int check_prep_size(int Cout, int Cin, int KH, int KW, long long ld_out, int mode, const char* who) {
+  B200_CHECK_ARG(prep_total(Cout, Cin, KH, KW, ld_out, mode) < (1LL << 31) && (long long)Cout * ld_out < (1LL << 31),
+                 "%s: weight tensor too large", who);
+  return 0;
+}
 static long long prep_total(int Cout, int Cin, int KH, int KW, long long ld_out, int mode) {
   if ((mode & 0xff) == 4) {
     const int S = mode >> 8;
@@ -993,7 +1022,8 @@ static long long prep_total(int Cout, int Cin, int KH, int KW, long long ld_out,
 int b200ddp_conv2d_weight_prep(const float* w, float* out, int Cout, int Cin, int KH, int KW, long long ld_out, int mode,
                                int device, void* stream) {
   B200_CHECK_ARG(w && out && Cout > 0 && Cin > 0 && KH > 0 && KW > 0, "conv2d_weight_prep: bad argument");
-  const int rc_mode = check_prep_mode(Cout, Cin, KH, KW, ld_out, mode, "conv2d_weight_prep");
+  int rc_mode = check_prep_mode(Cout, Cin, KH, KW, ld_out, mode, "conv2d_weight_prep");
+  if (!rc_mode) rc_mode = check_prep_size(Cout, Cin, KH, KW, ld_out, mode, "conv2d_weight_prep");
   if (rc_mode) return rc_mode;
   B200_DEVICE(device);
   const long long total = prep_total(Cout, Cin, KH, KW, ld_out, mode);
@@ -1012,7 +1042,8 @@ int b200ddp_conv2d_weight_prep_multi(const b200ddp_weight_prep_job* jobs, int nj
   for (int j = 0; j < njobs; ++j) {
     const b200ddp_weight_prep_job& q = jobs[j];
     B200_CHECK_ARG(q.w && q.out && q.Cout > 0 && q.Cin > 0 && q.KH > 0 && q.KW > 0, "conv2d_weight_prep_multi: job %d: bad argument", j);
-    const int rc_mode = check_prep_mode(q.Cout, q.Cin, q.KH, q.KW, q.ld_out, q.mode, "conv2d_weight_prep_multi");
+    int rc_mode = check_prep_mode(q.Cout, q.Cin, q.KH, q.KW, q.ld_out, q.mode, "conv2d_weight_prep_multi");
+    if (!rc_mode) rc_mode = check_prep_size(q.Cout, q.Cin, q.KH, q.KW, q.ld_out, q.mode, "conv2d_weight_prep_multi");
     if (rc_mode) return rc_mode;
     const long long total = prep_total(q.Cout, q.Cin, q.KH, q.KW, q.ld_out, q.mode);
     long long want = (total + 1023) / 1024;                      // ~4 elements per thread
