@@ -270,3 +270,35 @@ def test_accelerator_single_process(tmp_path, monkeypatch):
     from safetensors.torch import load_file
     sd = load_file(str(tmp_path / "model.safetensors"))
     assert set(sd) == set(m.state_dict()) and not any(k.startswith("module.") for k in sd)
+
+
+def test_sm_budget_drives_the_one_wave_grid_plans():
+    """b200ddp_set_sm_budget: the wgrad planner splits the pixel range so that tiles x splits fits the SMs it may
+    count on; the DDP wrapper lowers the budget by the number of NCCL channels. Host-only
+    entry points, no GPU needed: the workspace query exposes the split count."""
+    L = _lib.load()
+    prev = L.b200ddp_set_sm_budget(148)
+    try:
+        # conv2 of the toy model: Cin=64, 27x27, Cout=192, 5x5: K = 1600 -> 7 row tiles of 256, one channel tile
+        full = int(L.b200ddp_conv2d_wgrad_workspace_bytes(128, 64, 27, 27, 192, 5, 5, 1, 2))
+        assert full == (148 // 7) * 192 * 1600 * 4
+        assert L.b200ddp_set_sm_budget(132) == 148
+        less = int(L.b200ddp_conv2d_wgrad_workspace_bytes(128, 64, 27, 27, 192, 5, 5, 1, 2))
+        assert less == (132 // 7) * 192 * 1600 * 4
+        assert L.b200ddp_set_sm_budget(0) == 132          # 0 = all SMs again
+        assert int(L.b200ddp_conv2d_wgrad_workspace_bytes(128, 64, 27, 27, 192, 5, 5, 1, 2)) == full
+        assert L.b200ddp_set_sm_budget(4) == 148          # clamped to a sane minimum
+        assert L.b200ddp_set_sm_budget(148) == 16
+    finally:
+        L.b200ddp_set_sm_budget(prev)
+
+
+def test_space_to_depth_geometry_and_opt_in(monkeypatch):
+    from b200ddp import nn as bnn
+    # conv1 of the toy model: 224 -> 55 outputs, 11x11 stride 4 becomes 3x3 over a 57x57 grid
+    assert bnn._s2d_geometry(224, 224, 11, 11, 4, 2) == (55, 55, 3, 3, 57, 57)
+    monkeypatch.delenv("B200DDP_CONV1_S2D", raising=False)
+    assert not bnn._use_s2d(3, 11, 11, 4)                 # measured: no net gain, so off unless asked for
+    monkeypatch.setenv("B200DDP_CONV1_S2D", "1")
+    assert bnn._use_s2d(3, 11, 11, 4)
+    assert not bnn._use_s2d(64, 5, 5, 1) and not bnn._use_s2d(16, 11, 11, 4)     # stride 1 / too many channels
