@@ -183,7 +183,7 @@ int b200ddp_relu_maxpool_bwd(const float* dy, const unsigned char* idx, float* d
  * they compute (torch: aten::convolution_backward's grad_bias = dY.sum((0,2,3)), reached from reference :125):
  * db[c] = sum over batch and plane of dx. Per-plane sums in fp64 scratch, folded over the batch in a fixed order by
  * a second small kernel (deterministic). scratch: b200ddp_bias_grad_scratch_bytes(B, C) bytes, 8-byte aligned, need
- * not be initialised. relu_bwd_bias: dx = dy * (y > 0) on [B][C][HW], HW <= 4096. */
+ * not be initialised. relu_bwd_bias: dx = dy * (y > 0) on [B][C][HW]. */
 long long b200ddp_bias_grad_scratch_bytes(int B, int C);
 int b200ddp_relu_maxpool_bwd_bias(const float* dy, const unsigned char* idx, float* dx, float* db, int B, int C, int H,
                                   int W, void* scratch, long long scratch_bytes, int device, void* stream);

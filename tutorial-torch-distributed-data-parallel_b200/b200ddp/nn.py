@@ -362,7 +362,7 @@ class _Conv2dFn(torch.autograd.Function):
                                                       st), "relu_maxpool_bwd")
         elif ctx.relu:
             dz = torch.empty_like(dy)
-            if want_db and OH * OW <= 4096:
+            if want_db:
                 _lib.check(L.b200ddp_relu_bwd_bias(dy.data_ptr(), aux.data_ptr(), dz.data_ptr(), db.data_ptr(), N, Cout,
                                                    OH * OW, scratch.data_ptr(), scratch.numel(), dev, st), "relu_bwd_bias")
                 have_db = True

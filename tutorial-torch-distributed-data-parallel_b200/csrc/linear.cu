@@ -356,16 +356,19 @@ __global__ void __launch_bounds__(256) linear_smalln_dw_kernel(const float* __re
   }
 }
 
-// dz = dy * gate-scale, db[n] = sum_b dz[b][n]. Block = 32 columns x 8 row lanes.
-__global__ void __launch_bounds__(256) gate_bias_bwd_kernel(const float* __restrict__ dy,
+// dz = dy * gate-scale, db[n] = sum_b dz[b][n]. Block = 32 columns x 32 row lanes (the kernel is a few MB of traffic:
+// latency bound, so as many independent loads in flight as possible).
+constexpr int kGbRows = 32;
+__global__ void __launch_bounds__(32 * kGbRows) gate_bias_bwd_kernel(const float* __restrict__ dy,
                                                             const unsigned char* __restrict__ gate, float drop_scale,
                                                             float* __restrict__ dz, float* __restrict__ db, int B, int N) {
-  __shared__ float red[8][33];
+  __shared__ float red[kGbRows][33];
   const int cx = threadIdx.x & 31, ry = threadIdx.x >> 5;
   const int n = blockIdx.x * 32 + cx;
   float s = 0.f;
   if (n < N) {
-    for (int b = ry; b < B; b += 8) {
+#pragma unroll 4
+    for (int b = ry; b < B; b += kGbRows) {
       const long long i = (long long)b * N + n;
       float v = dy[i];
       if (gate) {
@@ -381,7 +384,7 @@ __global__ void __launch_bounds__(256) gate_bias_bwd_kernel(const float* __restr
   if (ry == 0 && n < N && db) {
     float tot = 0.f;
 #pragma unroll
-    for (int j = 0; j < 8; ++j) tot += red[j][cx];
+    for (int j = 0; j < kGbRows; ++j) tot += red[j][cx];
     db[n] = tot;
   }
 }
@@ -486,7 +489,7 @@ int b200ddp_linear_bwd_dw(const float* dz, const float* x, float* dw, float* db,
     return 0;
   }
   if (db) {
-    gate_bias_bwd_kernel<<<ceil_div(N, 32), 256, 0, s>>>(dz, nullptr, 1.f, nullptr, db, B, N);
+    gate_bias_bwd_kernel<<<ceil_div(N, 32), 32 * kGbRows, 0, s>>>(dz, nullptr, 1.f, nullptr, db, B, N);
     B200_LAUNCH_OK();
   }
   Epilogue ep;
@@ -503,7 +506,7 @@ int b200ddp_gate_bias_bwd(const float* dy, const unsigned char* gate, float drop
   B200_CHECK_ARG(dy && B > 0 && N > 0 && (dz || db), "gate_bias_bwd: bad argument");
   B200_DEVICE(device);
   const float scale = dropout_p > 0.f ? 1.0f / (1.0f - dropout_p) : 1.0f;
-  gate_bias_bwd_kernel<<<ceil_div(N, 32), 256, 0, as_stream(stream)>>>(dy, gate, scale, dz, db, B, N);
+  gate_bias_bwd_kernel<<<ceil_div(N, 32), 32 * kGbRows, 0, as_stream(stream)>>>(dy, gate, scale, dz, db, B, N);
   B200_LAUNCH_OK();
   return 0;
 }

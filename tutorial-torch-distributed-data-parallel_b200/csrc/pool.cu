@@ -152,39 +152,36 @@ __global__ void __launch_bounds__(256) relu_maxpool_bwd_kernel(const float* __re
 }
 
 // dx = dy * (y > 0) for [B][C][HW] tensors plus the per-plane sums of dx, folded into db[c] by bias_fold_kernel (the
-// bias gradient of a convolution whose ReLU is fused into its epilogue). A CTA takes P whole planes (contiguous,
-// <= kReluChunk elements): a flat, coalesced elementwise pass that also parks dx in shared memory, then one warp
-// per plane adds its plane up from there.
-constexpr int kReluChunk = 4096;
+// bias gradient of a convolution whose ReLU is fused into its epilogue). One warp per plane, eight independent
+// (y, dy) load pairs in flight per lane, no shared memory, no block barriers.
 __global__ void __launch_bounds__(256) relu_bwd_bias_kernel(const float* __restrict__ dy, const float* __restrict__ y,
                                                             float* __restrict__ dx, double* __restrict__ plane_sums,
-                                                            int B, int C, int HW, int P) {
-  __shared__ float s_v[kReluChunk];
-  const long long planes = (long long)B * C;
-  const long long nchunks = (planes + P - 1) / P;
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
-  for (long long chunk = blockIdx.x; chunk < nchunks; chunk += gridDim.x) {
-    const long long pl0 = chunk * P;
-    const int np = (int)(planes - pl0 < P ? planes - pl0 : P);
-    const int n = np * HW;
-    const long long base = pl0 * HW;
-#pragma unroll 4
-    for (int i = threadIdx.x; i < n; i += blockDim.x) {
-      const float yv = __ldg(y + base + i), gv = __ldg(dy + base + i);     // both loads issued before the select
-      const float v = yv > 0.f ? gv : 0.f;
-      dx[base + i] = v;
-      s_v[i] = v;
-    }
-    __syncthreads();
-    for (int pl = warp; pl < np; pl += nwarps) {
-      float acc = 0.f;
-      for (int o = lane; o < HW; o += 32) acc += s_v[pl * HW + o];
-      double d = (double)acc;
+                                                            long long planes, int HW) {
+  const int lane = threadIdx.x & 31;
+  const long long nw = (long long)gridDim.x * (blockDim.x >> 5);
+  for (long long pl = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); pl < planes; pl += nw) {
+    const long long base = pl * HW;
+    float acc = 0.f;
+    for (int o0 = 0; o0 < HW; o0 += 256) {
+      float yv[8], gv[8];
 #pragma unroll
-      for (int sft = 16; sft > 0; sft >>= 1) d += __shfl_xor_sync(0xffffffffu, d, sft);
-      if (lane == 0) plane_sums[pl0 + pl] = d;
+      for (int u = 0; u < 8; ++u) {
+        const int o = o0 + u * 32 + lane;
+        yv[u] = o < HW ? __ldg(y + base + o) : 0.f;
+        gv[u] = o < HW ? __ldg(dy + base + o) : 0.f;
+      }
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int o = o0 + u * 32 + lane;
+        const float v = yv[u] > 0.f ? gv[u] : 0.f;
+        if (o < HW) dx[base + o] = v;
+        acc += v;
+      }
     }
-    __syncthreads();
+    double d = (double)acc;
+#pragma unroll
+    for (int sft = 16; sft > 0; sft >>= 1) d += __shfl_xor_sync(0xffffffffu, d, sft);
+    if (lane == 0) plane_sums[pl] = d;
   }
 }
 
@@ -298,16 +295,15 @@ int b200ddp_relu_maxpool_bwd_bias(const float* dy, const unsigned char* idx, flo
 int b200ddp_relu_bwd_bias(const float* dy, const float* y, float* dx, float* db, int B, int C, int HW, void* scratch,
                           long long scratch_bytes, int device, void* stream) {
   B200_CHECK_ARG(dy && y && dx && db && B > 0 && C > 0 && HW > 0, "relu_bwd_bias: bad argument");
-  B200_CHECK_ARG(HW <= kReluChunk, "relu_bwd_bias: plane of %d elements exceeds %d", HW, kReluChunk);
+
   B200_CHECK_ARG(scratch && ((uintptr_t)scratch & 7) == 0 && scratch_bytes >= (long long)B * C * 8,
                  "relu_bwd_bias: scratch too small or unaligned (need %lld bytes, 8-byte aligned)", (long long)B * C * 8);
   B200_DEVICE(device);
   const long long planes = (long long)B * C;
-  const int P = kReluChunk / HW;
-  const long long want = (planes + P - 1) / P;
-  const int grid = (int)(want < (long long)kNumSMs * 8 ? want : (long long)kNumSMs * 8);
+  const long long want = (planes + 7) / 8;                 // 8 warps per CTA, one plane per warp and pass
+  const int grid = (int)(want < (long long)kNumSMs * 16 ? want : (long long)kNumSMs * 16);
   double* plane_sums = reinterpret_cast<double*>(scratch);
-  relu_bwd_bias_kernel<<<grid, 256, 0, as_stream(stream)>>>(dy, y, dx, plane_sums, B, C, HW, P);
+  relu_bwd_bias_kernel<<<grid, 256, 0, as_stream(stream)>>>(dy, y, dx, plane_sums, planes, HW);
   B200_LAUNCH_OK();
   bias_fold_kernel<<<(C + 7) / 8, 256, 0, as_stream(stream)>>>(plane_sums, db, B, C);
   B200_LAUNCH_OK();
