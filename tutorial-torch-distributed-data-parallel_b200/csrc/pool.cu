@@ -91,8 +91,8 @@ __global__ void __launch_bounds__(256) relu_maxpool_bwd_kernel(const float* __re
                                                                const unsigned char* __restrict__ idx,
                                                                float* __restrict__ dx, double* __restrict__ plane_sums,
                                                                int B, int C, int H, int W, int OH, int OW, int P) {
-  __shared__ float s_dy[kPoolChunk];
-  __shared__ unsigned char s_idx[kPoolChunk];
+  __shared__ float s_dy[kPoolChunk + 1];              // [n_in] = dummy entry (gradient 0, slot 255) for windows that
+  __shared__ unsigned char s_idx[kPoolChunk + 4];     // do not exist: no predicated loads in the quad loop
   const int ohw = OH * OW, hw = H * W;
   const long long planes = (long long)B * C;
   const long long nchunks = (planes + P - 1) / P;
@@ -108,6 +108,7 @@ __global__ void __launch_bounds__(256) relu_maxpool_bwd_kernel(const float* __re
       s_dy[i] = __ldg(dyp + i);
       s_idx[i] = __ldg(ip + i);
     }
+    if (threadIdx.x == 0) { s_dy[n_in] = 0.f; s_idx[n_in] = 255; }
     __syncthreads();
     if (plane_sums) {
       for (int pl = warp; pl < np; pl += nwarps) {
@@ -127,15 +128,12 @@ __global__ void __launch_bounds__(256) relu_maxpool_bwd_kernel(const float* __re
     Walk3 wk(threadIdx.x, blockDim.x, QH, QW);
     for (int i = threadIdx.x; i < n_quads; i += blockDim.x, wk.next()) {
       const int pl = wk.pl, a = wk.r, bq = wk.c;
-      const float* sd = s_dy + pl * ohw;
-      const unsigned char* si = s_idx + pl * ohw;
       const bool va = a < OH, vb = bq < OW, va0 = a > 0, vb0 = bq > 0;
-      float d11 = 0.f, d10 = 0.f, d01 = 0.f, d00 = 0.f;
-      int c11 = 255, c10 = 255, c01 = 255, c00 = 255;
-      if (va && vb) { d11 = sd[a * OW + bq]; c11 = si[a * OW + bq]; }
-      if (va && vb0) { d10 = sd[a * OW + bq - 1]; c10 = si[a * OW + bq - 1]; }
-      if (va0 && vb) { d01 = sd[(a - 1) * OW + bq]; c01 = si[(a - 1) * OW + bq]; }
-      if (va0 && vb0) { d00 = sd[(a - 1) * OW + bq - 1]; c00 = si[(a - 1) * OW + bq - 1]; }
+      const int base = pl * ohw + a * OW + bq;                         // window (a, bq) of this plane
+      const int i11 = (va && vb) ? base : n_in, i10 = (va && vb0) ? base - 1 : n_in;
+      const int i01 = (va0 && vb) ? base - OW : n_in, i00 = (va0 && vb0) ? base - OW - 1 : n_in;
+      const float d11 = s_dy[i11], d10 = s_dy[i10], d01 = s_dy[i01], d00 = s_dy[i00];
+      const int c11 = s_idx[i11], c10 = s_idx[i10], c01 = s_idx[i01], c00 = s_idx[i00];
       const float g00 = (c11 == 0 ? d11 : 0.f) + (c10 == 2 ? d10 : 0.f) + (c01 == 6 ? d01 : 0.f) + (c00 == 8 ? d00 : 0.f);
       const float g01 = (c11 == 1 ? d11 : 0.f) + (c01 == 7 ? d01 : 0.f);
       const float g10 = (c11 == 3 ? d11 : 0.f) + (c10 == 5 ? d10 : 0.f);
