@@ -489,7 +489,7 @@ def prepare_conv_weights(convs, first_needs_dgrad: bool = False) -> None:
         if not conv.weight.is_cuda or conv.weight.dtype != torch.float32 or not conv.weight.is_contiguous():
             conv._prepared = None
             continue
-        j, prepared = conv._prep_jobs(need_dgrad=(i > 0 or first_needs_dgrad))
+        j, prepared = conv._prep_jobs(need_dgrad=torch.is_grad_enabled() and (i > 0 or first_needs_dgrad))
         jobs += j
         conv._prepared = prepared
     dev = convs[0].weight.device
