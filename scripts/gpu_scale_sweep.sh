@@ -3,9 +3,9 @@
 N=${1:-8}
 mkdir -p gpurun_out
 export PYTHONUNBUFFERED=1
-for CH in 16 24 32 12; do
+for CH in 8 16 24 32; do
   export NCCL_MAX_NCHANNELS=$CH
-  if [ "$CH" = "16" ]; then export NCCL_DEBUG=INFO; export NCCL_DEBUG_SUBSYS=INIT,COLL,TUNING; else unset NCCL_DEBUG; unset NCCL_DEBUG_SUBSYS; fi
+  unset NCCL_DEBUG; unset NCCL_DEBUG_SUBSYS
   timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29511 \
       bench.py --gpus $N --steps 30 --warmup 5 --no-cpu-baseline > gpurun_out/bench_n${N}_ch$CH.log 2>&1
   echo "channels=$CH rc=$? $(grep -h '^{' gpurun_out/bench_n${N}_ch$CH.log | python -c 'import sys,json; d=json.loads(sys.stdin.readline()); print(round(d["value"]), "samples/s", round(d["ms_per_step"],3), "ms/step")' 2>/dev/null)"
