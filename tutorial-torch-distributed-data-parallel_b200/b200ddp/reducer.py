@@ -112,6 +112,22 @@ class Reducer:
         self._callback_queued = False
         self._ready_order: List[int] = []
         self.first_ready_order: Optional[List[int]] = None
+        # Early launch inside the LAST bucket: its final members (the first layer's weight and bias) become ready only
+        # when the whole backward pass is over, so a bucket-granular launch leaves the all-reduce of everything else in
+        # that bucket (the other conv layers, ~10 MB) exposed after the last kernel. The bucket stays one bucket (same
+        # plan and sizes as the reference's reducer); its all-reduce is issued as two ranges: the prefix as soon as its
+        # members are ready - it then runs under the first layer's weight-gradient kernel - and the tail at the end.
+        self._tail_prefix = None           # (bucket index, set of prefix members, prefix end offset)
+        self._tail_prefix_pending = 0
+        self._tail_early = False
+        if (self.cuda and self.world > 1 and self.clip_value is None and self.clip_norm is None and self.buckets
+                and os.environ.get("B200DDP_TAIL_SPLIT", "1") != "0"):
+            last = self.buckets[-1]
+            if len(last.members) > 2:
+                prefix = last.members[:-2]
+                p_start, p_end = arena.span(prefix[0], prefix[-1])
+                if (p_end - p_start) * 4 >= (1 << 20):
+                    self._tail_prefix = (last.index, frozenset(prefix), p_end)
         if self.cuda:
             dev = arena.device
             self._sq = torch.zeros(1, dtype=torch.float32, device=dev)
@@ -148,6 +164,8 @@ class Reducer:
         self.next_bucket = 0
         self._callback_queued = False
         self._ready_order = []
+        self._tail_early = False
+        self._tail_prefix_pending = len(self._tail_prefix[1]) if self._tail_prefix is not None else 0
 
     def _on_grad_ready(self, i: int, param) -> None:
         if not self.require_sync:
@@ -175,6 +193,16 @@ class Reducer:
             param.grad = view
         b = self.buckets[self.bucket_of[i]]
         b.pending -= 1
+        if self._tail_prefix is not None and b.index == self._tail_prefix[0] and i in self._tail_prefix[1]:
+            self._tail_prefix_pending -= 1
+            if (self._tail_prefix_pending == 0 and not self._tail_early and b.pending > 0
+                    and self.next_bucket == b.index):      # every earlier bucket is already on the comm stream
+                from .nn import join_side_work
+                join_side_work(self.arena.device)
+                self._tail_early = True
+                self.comm.bucket_reduce_launch(self.arena.g_flat[b.start:self._tail_prefix[2]].data_ptr(),
+                                               self._tail_prefix[2] - b.start,
+                                               1.0 if self.pass_prescaled else 1.0 / self.world, self.arena.device)
         if b.pending == 0:
             b.ready = True
             while self.next_bucket < len(self.buckets) and self.buckets[self.next_bucket].ready:
@@ -216,7 +244,9 @@ class Reducer:
         t = self._bucket_tensor(b)
         if self.cuda:
             premul = 1.0 if self.pass_prescaled else 1.0 / self.world
-            self.comm.bucket_reduce_launch(t.data_ptr(), b.end - b.start, premul, t.device)
+            if self._tail_early and self._tail_prefix is not None and b.index == self._tail_prefix[0]:
+                t = self.arena.g_flat[self._tail_prefix[2]:b.end]      # the prefix is already being reduced
+            self.comm.bucket_reduce_launch(t.data_ptr(), t.numel(), premul, t.device)
         else:
             t.mul_(1.0 / self.world)
             b.work = dist.all_reduce(t, group=self.pg, async_op=True)
