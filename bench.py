@@ -361,6 +361,11 @@ def run_b200(args) -> None:
             dist.barrier()
             torch.cuda.synchronize(dev)
 
+    # Reserve the activation pool up front: one 24 GB block that the caching allocator then carves up, so that no
+    # cudaMalloc (tens of ms for multi-hundred-MB segments, observed as single 30-65 ms steps among 2.34 ms ones)
+    # happens inside a timed region. 180 GB of HBM per GPU: this is 13 % of it.
+    b200ddp.reserve_memory_pool(float(os.environ.get("B200DDP_BENCH_RESERVE_GB", "24")), dev)
+
     # ---- warm-up -----------------------------------------------------------------------------------------------
     for i in range(args.warmup):
         step_resident(i)
@@ -396,6 +401,7 @@ def run_b200(args) -> None:
     ms = ev0.elapsed_time(ev1)
     final_loss = float(loss.detach())
     adam_ms = [a.elapsed_time(b) for a, b in adam_ev]
+    step_ms = [adam_ev[k][0].elapsed_time(adam_ev[k + 1][0]) for k in range(len(adam_ev) - 1)]    # step-to-step period
     t = torch.tensor([ms], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -495,6 +501,9 @@ def run_b200(args) -> None:
             "dtype": "tf32" if args.mode == "tf32" else "fp32", "data": "synthetic",
             "config": workload_config(args),
             "clocks": clock_info,
+            "step_ms_percentiles": ({"p10": sorted(step_ms)[len(step_ms) // 10], "p50": sorted(step_ms)[len(step_ms) // 2],
+                                     "p90": sorted(step_ms)[(len(step_ms) * 9) // 10], "max": max(step_ms),
+                                     "slowest_step_index": step_ms.index(max(step_ms))} if step_ms else None),
             "e2e": {"value": world * B * args.steps / (e2e_ms_max * 1e-3), "unit": "samples/s",
                     "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "ms_per_step": e2e_ms_max / args.steps,
                     "wall_ms_per_step": 1e3 * e2e_wall / args.steps},

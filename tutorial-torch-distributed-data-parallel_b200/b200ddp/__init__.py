@@ -24,6 +24,19 @@ from .sampler import DistributedSampler  # noqa: F401
 
 convert_sync_batchnorm = SyncBatchNorm.convert_sync_batchnorm
 
-__all__ = ["DistributedDataParallel", "DistributedSampler", "SyncBatchNorm", "convert_sync_batchnorm", "Adam",
+
+def reserve_memory_pool(gigabytes: float = 24.0, device=None) -> None:
+    """Have torch's caching allocator hold one block of `gigabytes` from the start, which it then carves up for the
+    step's activations and workspaces. Without it the allocator grows by cudaMalloc calls during the first few hundred
+    steps, and a cudaMalloc of a multi-hundred-MB segment stalls the launching thread for 30-65 ms (measured: single
+    steps of 31 and 65 ms among 2.34 ms ones). 180 GB of HBM per B200 make the reservation cheap."""
+    import torch
+    if gigabytes <= 0 or not torch.cuda.is_available():
+        return
+    dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+    blk = torch.empty(int(gigabytes * (1 << 30)), dtype=torch.uint8, device=dev)
+    del blk
+
+__all__ = ["reserve_memory_pool", "DistributedDataParallel", "DistributedSampler", "SyncBatchNorm", "convert_sync_batchnorm", "Adam",
            "CrossEntropyLoss", "FlatArena", "nn", "optim"]
 __version__ = "0.1.0"
