@@ -112,10 +112,38 @@ int b200ddp_gate_bias_bwd(const float* dy, const unsigned char* gate, float drop
                           int N, int device, void* stream);
 
 /* ---- F3: loss ---------------------------------------------------------------------------------------- */
-/* Replaces nn.CrossEntropyLoss() (reference :248,:122): loss[0] = mean CE, dlogits (nullable) =
- * (softmax - onehot)/B. labels int64. err_flag_dev (nullable) set to 1 on an out-of-range label. */
+/* Replaces nn.CrossEntropyLoss() (reference :248,:122): loss[0] = mean CE over the rows whose label is not
+ * ignore_index (-100, torch's default), dlogits (nullable) = (softmax - onehot)/n_valid, zero rows for ignored
+ * labels. labels int64. A label outside [0, C) other than -100 sets err_flag_dev (nullable; may be mapped host
+ * memory) to 1 and is treated as ignored: its gradient row is zero, never uninitialised. */
 int b200ddp_softmax_ce(const float* logits, const long long* labels, float* loss, float* dlogits, int B, int C,
                        int* err_flag_dev, int device, void* stream);
+
+/* ---- f1: evaluate() ------------------------------------------------------------------------------------- */
+/* Replaces, per test batch of reference evaluate() (multi-GPU-training-torch.py:136-153, -accelerate.py:60-75), the
+ * head Linear (classifier.6) + criterion + loss.item() + torch.max(outputs, 1) + (predicted == labels).sum().item():
+ * metrics[0] += sum_i CE_i, metrics[1] += #(argmax_i == y_i), metrics[2] += B — on the device, no host sync.
+ * h [B][K] (input of the head), w [N][K], bias [N] or null, N <= 16, labels int64; logits_out [B][N] nullable.
+ * scratch: b200ddp_eval_scratch_bytes(B) bytes, 256-byte aligned, first 4 bytes zero before the first call
+ * (the kernel resets them). Deterministic (row results summed in row order by the last CTA). */
+long long b200ddp_eval_scratch_bytes(int B);
+int b200ddp_head_eval(const float* h, const float* w, const float* bias, const long long* labels, float* logits_out, int B,
+                      int N, int K, float* metrics, void* scratch, long long scratch_bytes, int device, void* stream);
+/* Same three sums from logits [B][C] that already exist (any model). */
+int b200ddp_logits_eval(const float* logits, const long long* labels, int B, int C, float* metrics, void* scratch,
+                        long long scratch_bytes, int device, void* stream);
+
+/* ---- f2: input transform --------------------------------------------------------------------------------- */
+/* Replaces transforms.Resize -> RandomHorizontalFlip -> ToTensor -> Normalize of reference data_and_toy_model.py:13-36
+ * (PIL on DataLoader workers) and the 77 MB blocking H2D of multi-GPU-training-torch.py:110: the batch arrives as the
+ * dataset stores it, img uint8 [B][H][W][3], and out fp32 [B][3][OH][OW] is bit-identical to the torchvision result
+ * (Pillow's two-pass 8-bit bilinear resample, then x/255, then (x - mean)/std). flip [B] bytes (nullable): 1 = mirror
+ * the resized image. tab_h / tab_v: DEVICE tables from b200ddp_resize_coeffs for (W -> OW) and (H -> OH);
+ * mean3 / std3: HOST arrays of 3 floats. Enlargements only (H <= OH <= 512, H, W <= 64). */
+int b200ddp_resize_coeffs(int in_size, int out_size, int* table_host /* 5 * out_size ints: first index | taps | 3 coefs */);
+int b200ddp_image_transform(const unsigned char* img, const unsigned char* flip, float* out, int B, int H, int W, int OH,
+                            int OW, const int* tab_h, const int* tab_v, const float* mean3, const float* std3, int device,
+                            void* stream);
 
 /* ---- C1-C5: convolutions ------------------------------------------------------------------------------ */
 /* Replace nn.Conv2d forward / backward (cuDNN TF32 implicit GEMM + NCHW<->NHWC conversions) of torchvision
@@ -136,6 +164,15 @@ long long b200ddp_conv2d_wgrad_workspace_bytes(int Nb, int Cin, int H, int W, in
 int b200ddp_conv2d_wgrad(const float* x, const float* dy, float* dw, const int* ktab, int k_order, int Nb, int Cin, int H,
                          int W, int Cout, int KH, int KW, int stride, int pad, void* ws, long long ws_bytes, int device,
                          void* stream);
+/* Strict mode of the same three operations ("rtol 1e-5 strict" against torch with
+ * torch.backends.cudnn.allow_tf32 = False): direct fp32 SIMT convolutions, no TF32 rounding, fp64 across partial rows,
+ * deterministic. w / dw in torch's [Cout][Cin][KH][KW] layout, any stride / padding. Exactness path, not a fast one. */
+int b200ddp_conv2d_fwd_fp32(const float* x, const float* w, const float* bias, float* y, int Nb, int Cin, int H, int W,
+                            int Cout, int KH, int KW, int stride, int pad, int relu, int device, void* stream);
+int b200ddp_conv2d_dgrad_fp32(const float* dy, const float* w, float* dx, int Nb, int Cin, int H, int W, int Cout, int KH,
+                              int KW, int stride, int pad, int device, void* stream);
+int b200ddp_conv2d_wgrad_fp32(const float* x, const float* dy, float* dw, int Nb, int Cin, int H, int W, int Cout, int KH,
+                              int KW, int stride, int pad, int device, void* stream);
 /* mode 0: out[co][0..ld_out) = w[co][:] zero padded; mode 1: flipped / transposed weights for dgrad,
  * out[ci][co*KH*KW + (KH-1-kh)*KW + (KW-1-kw)] = w[co][ci][kh][kw], row stride ld_out; modes 2 / 3: the same two
  * matrices with the reduction index in channel-block-major order (k_order 1). */

@@ -308,3 +308,19 @@ def syncbn_backward(dys: Sequence[np.ndarray], xs: Sequence[np.ndarray], weight,
     gws = [(s * invstd).astype(np.float32) for s in sum_dy_xmu_r]
     gbs = [s.astype(np.float32) for s in sum_dy_r]
     return dxs, gws, gbs
+
+
+# ---- f1: evaluate() -------------------------------------------------------------------------------------------------
+def evaluate_batches(logits_per_batch: Sequence[np.ndarray], labels_per_batch: Sequence[np.ndarray]):
+    """Reference evaluate() (multi-GPU-training-torch.py:136-153) given each batch's logits:
+    total_test_loss += mean CE * batch_size; predicted = argmax (first maximum, torch.max); correct += (pred == y).
+    Returns (total_test_loss, correct, total) as Python floats."""
+    total_loss, correct, total = 0.0, 0.0, 0.0
+    for z, y in zip(logits_per_batch, labels_per_batch):
+        loss, _ = softmax_ce(z, y)
+        bs = z.shape[0]
+        total_loss += float(loss) * bs
+        pred = np.argmax(z, axis=1)              # numpy argmax = first maximal index, like torch.max
+        correct += float((pred == y).sum())
+        total += bs
+    return total_loss, correct, total

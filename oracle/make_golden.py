@@ -261,6 +261,66 @@ def gen_trace():
     json.dump(out, open(os.path.join(GOLD, "trace.json"), "w"), indent=1)
 
 
+def gen_eval():
+    """The reference's own evaluate() (multi-GPU-training-torch.py:136-153) on CPU: 20 samples in batches of 8 (last one
+    ragged), AlexNet-10 seed 1234 in eval mode. Records the hidden activations entering the head, the head's weights,
+    logits and labels per batch, and evaluate()'s three totals; asserts the restatement returns the same."""
+    ref = _load_reference()
+    model = rl.make_model(seed=1234, dropout=0.5)
+    x, y = rl.synthetic_pool(20, seed=11)
+    model.eval()
+    with torch.no_grad():                             # an untrained model predicts one class: make every other label a hit
+        pred = model(x).argmax(1)
+    y = torch.where(torch.arange(20) % 2 == 0, pred, (pred + 1) % 10)
+    ds = torch.utils.data.TensorDataset(x, y)
+    loader = torch.utils.data.DataLoader(ds, batch_size=8)
+    hid, logits = [], []
+    def _grab(m, i, o):
+        hid.append(i[0].detach().numpy().copy())
+        logits.append(o.detach().numpy().copy())
+    h1 = model.classifier[6].register_forward_hook(_grab)
+    crit = nn.CrossEntropyLoss()
+    tl, c, n = ref.evaluate(model, loader, crit, torch.device("cpu"))
+    h1.remove()
+    tl2, c2, n2 = rl.evaluate_epoch(model, loader, crit, torch.device("cpu"))
+    assert float(tl) == float(tl2) and float(c) == float(c2) and float(n) == float(n2)
+    np.savez_compressed(os.path.join(GOLD, "eval.npz"),
+                        hidden=np.concatenate(hid), logits=np.concatenate(logits), labels=y.numpy(),
+                        w=model.classifier[6].weight.detach().numpy(), b=model.classifier[6].bias.detach().numpy(),
+                        batch=np.int64(8), total_test_loss=np.float32(tl.item()), correct=np.float32(c.item()),
+                        total=np.float32(n.item()))
+    print("eval", float(tl), float(c), float(n))
+
+
+def gen_input_pipeline():
+    """The real transform of reference data_and_toy_model.py:13-36 (torchvision 0.26 + Pillow) on CIFAR-shaped uint8
+    images: the uint8 result of Resize(224), the first 16 rows of the final float tensor, and a sha256 of every full
+    float output (the GPU kernel is bit-exact, so a hash pins the full size)."""
+    import torchvision.transforms as T
+    from PIL import Image
+    mean, std = (0.4914, 0.4822, 0.4465), (0.2023, 0.1994, 0.2010)
+    rng = np.random.default_rng(32)
+    imgs = rng.integers(0, 256, (4, 32, 32, 3), dtype=np.uint8)
+    imgs[2] = 255                                     # saturated image
+    imgs[3, :, :16] = 0                               # hard vertical edge
+    flips = np.array([0, 1, 0, 1], np.uint8)
+    tail = T.Compose([T.ToTensor(), T.Normalize(mean, std)])
+    resized, rows, hashes = [], [], []
+    for i in range(4):
+        im = T.Resize(224)(Image.fromarray(imgs[i]))
+        resized.append(np.asarray(im).copy())
+        if flips[i]:
+            im = T.functional.hflip(im)                # RandomHorizontalFlip's action when it fires
+        out = tail(im).numpy()
+        rows.append(out[:, :16, :].copy())
+        hashes.append(hashlib.sha256(np.ascontiguousarray(out).tobytes()).hexdigest())
+    import PIL
+    import torchvision
+    np.savez_compressed(os.path.join(GOLD, "input_pipeline.npz"), images=imgs, flips=flips, resized_u8=np.stack(resized),
+                        first_rows=np.stack(rows), sha256=np.array(hashes),
+                        versions=np.array([f"torchvision {torchvision.__version__}", f"Pillow {PIL.__version__}"]))
+
+
 def gen_philox():
     kat = [{"ctr": [0, 0, 0, 0], "key": [0, 0], "out": [0x6627e8d5, 0xe169c58d, 0xbc57ac4c, 0x9b00dbd8]},
            {"ctr": [0xffffffff] * 4, "key": [0xffffffff] * 2, "out": [0x408f276d, 0x41c83b0e, 0xa20bc7c6, 0x6d5451fd]},
@@ -272,7 +332,7 @@ def gen_philox():
 
 if __name__ == "__main__":
     os.makedirs(GOLD, exist_ok=True)
-    which = sys.argv[1:] or ["sampler", "buckets", "adam", "clip", "layers", "philox", "trace"]
+    which = sys.argv[1:] or ["sampler", "buckets", "adam", "clip", "layers", "philox", "trace", "eval", "input_pipeline"]
     for w in which:
         globals()["gen_" + w]()
         print("wrote", w, flush=True)

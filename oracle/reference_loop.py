@@ -9,6 +9,7 @@ What it restates (reference = /root/reference, absent on the GPU box, so nothing
                             (patch 3; CIFAR-10 cannot be downloaded)
   * `train`                 multi-GPU-training-torch.py:104-133 -> train_epoch(): same statement order
                             (H2D no-op on CPU, zero_grad, forward, criterion, backward, step, loss.item())
+  * `evaluate`              multi-GPU-training-torch.py:136-153 -> evaluate_epoch(): same statement order
   * `basic_DDP_training_loop` :228-266                    -> ddp_worker(): setup (gloo), seeds, sampler,
                             stock DistributedDataParallel, CrossEntropyLoss, Adam(lr)
 Everything numeric is stock torch / torchvision on the host cores: that IS the reference's CPU path.
@@ -70,6 +71,25 @@ def train_epoch(model, loader, criterion: Callable, optimizer, device, max_steps
         if max_steps is not None and batch_idx >= max_steps:
             break
     return total_running_loss, n_samples
+
+
+def evaluate_epoch(model, loader, criterion: Callable, device):
+    """Statement-for-statement restatement of reference evaluate() (multi-GPU-training-torch.py:136-153)."""
+    model.eval()
+    correct = torch.zeros(1, device=device)
+    total = torch.zeros(1, device=device)
+    total_test_loss = torch.zeros(1, device=device)
+    with torch.no_grad():
+        for inputs, labels in loader:
+            inputs, labels = inputs.to(device), labels.to(device)
+            outputs = model(inputs)
+            loss = criterion(outputs, labels)
+            batch_size = torch.tensor(inputs.shape[0], device=device)
+            total_test_loss += loss.item() * batch_size
+            _, predicted = torch.max(outputs.data, 1)
+            total += batch_size
+            correct += (predicted == labels).sum().item()
+    return total_test_loss, correct, total
 
 
 def time_cpu_train(batch: int = 128, steps: int = 3, warmup: int = 1, threads: Optional[int] = None,

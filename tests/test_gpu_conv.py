@@ -208,3 +208,72 @@ def test_conv_table_order_path_on_wide_layers(layer, monkeypatch):
     assert _err(y.detach(), y64.detach()) < TOL
     assert _err(conv.weight.grad, w64.grad) < TOL
     assert _err(x.grad, x64.grad) < TOL
+
+
+# ---- bench-shape parity: every layer at batch 128, under the grid plans of both SM budgets -------
+@pytest.fixture
+def sm_budget(request):
+    L = _lib.load()
+    prev = L.b200ddp_set_sm_budget(request.param)
+    yield request.param
+    L.b200ddp_set_sm_budget(0 if prev >= 148 else prev)
+
+
+@pytest.mark.parametrize("sm_budget", [148, 132], indirect=True)
+@pytest.mark.parametrize("layer", [1, 2, 3, 4])
+def test_conv_batch128_fwd_dgrad_wgrad_match_float64(layer, sm_budget):
+    """conv2..conv5 forward / dgrad / wgrad at the bench's batch of 128, with the one-wave grid plans sized for all 148
+    SMs (single GPU) and for the 132 SMs left beside a 16-channel collective (every multi-GPU run)."""
+    Cin, H, Cout, K, s, p = LAYERS[layer]
+    torch.manual_seed(500 + layer)
+    x = torch.randn(128, Cin, H, H, device=DEV, requires_grad=True)
+    conv = bnn.Conv2d(Cin, Cout, K, stride=s, padding=p).to(DEV)
+    y = conv(x)
+    dy = torch.randn_like(y)
+    y.backward(dy)
+    x64 = x.detach().double().requires_grad_()
+    w64 = conv.weight.detach().double().requires_grad_()
+    b64 = conv.bias.detach().double().requires_grad_()
+    y64 = torch.nn.functional.conv2d(x64, w64, b64, stride=s, padding=p)
+    y64.backward(dy.double())
+    assert _err(y, y64.detach()) < TOL
+    assert _err(x.grad, x64.grad) < TOL
+    assert _err(conv.weight.grad, w64.grad) < TOL
+    assert _err(conv.bias.grad, b64.grad) < 1e-5
+
+
+@pytest.mark.parametrize("sm_budget", [132], indirect=True)
+def test_conv1_batch128_under_collective_budget(sm_budget):
+    torch.manual_seed(11)
+    x = torch.randn(128, 3, 224, 224, device=DEV)
+    conv = bnn.Conv2d(3, 64, 11, stride=4, padding=2).to(DEV)
+    y = conv(x)
+    dy = torch.randn_like(y)
+    y.backward(dy)
+    w64 = conv.weight.detach().double().requires_grad_()
+    b64 = conv.bias.detach().double().requires_grad_()
+    y64 = torch.nn.functional.conv2d(x.double(), w64, b64, stride=4, padding=2)
+    y64.backward(dy.double())
+    assert _err(y, y64.detach()) < TOL
+    assert _err(conv.weight.grad, w64.grad) < TOL
+
+
+# ---- strict mode (SURVEY 8(d) config 2): fp32 SIMT convolutions ------------------------------------------------------------
+@pytest.mark.parametrize("layer", range(5))
+def test_conv_strict_fp32_matches_float64(layer):
+    Cin, H, Cout, K, s, p = LAYERS[layer]
+    torch.manual_seed(700 + layer)
+    x = torch.randn(3, Cin, H, H, device=DEV, requires_grad=True)
+    conv = bnn.Conv2d(Cin, Cout, K, stride=s, padding=p, mode="fp32").to(DEV)
+    y = conv(x)
+    dy = torch.randn_like(y)
+    y.backward(dy)
+    x64 = x.detach().double().requires_grad_()
+    w64 = conv.weight.detach().double().requires_grad_()
+    b64 = conv.bias.detach().double().requires_grad_()
+    y64 = torch.nn.functional.conv2d(x64, w64, b64, stride=s, padding=p)
+    y64.backward(dy.double())
+    assert _err(y, y64.detach()) < 2e-6
+    assert _err(x.grad, x64.grad) < 2e-6          # stride 4 included: the strict dgrad has no stride limit
+    assert _err(conv.weight.grad, w64.grad) < 2e-6
+    assert _err(conv.bias.grad, b64.grad) < 1e-5

@@ -119,3 +119,50 @@ def test_syncbn_matches_global_batch_bn(golden_dir):
     np.testing.assert_allclose(np.concatenate(dxs), g["bn_dx"], rtol=1e-4, atol=1e-5)
     np.testing.assert_allclose(sum(gws), g["bn_gw"], rtol=1e-4, atol=1e-5)
     np.testing.assert_allclose(sum(gbs), g["bn_gb"], rtol=1e-4, atol=1e-5)
+
+
+def test_evaluate_restatement_matches_reference_evaluate(golden_dir):
+    """oracle.evaluate_batches against the totals the reference's own evaluate() returned (make_golden.gen_eval)."""
+    g = np.load(os.path.join(golden_dir, "eval.npz"))
+    bs = int(g["batch"])
+    z, y = g["logits"], g["labels"]
+    zs = [z[i:i + bs] for i in range(0, len(z), bs)]
+    ys = [y[i:i + bs] for i in range(0, len(y), bs)]
+    loss, correct, total = O.evaluate_batches(zs, ys)
+    assert abs(loss - float(g["total_test_loss"])) < 1e-5 * abs(float(g["total_test_loss"]))
+    assert correct == float(g["correct"]) == 10.0 and total == float(g["total"]) == 20.0
+    # the head restatement reproduces the recorded logits from the recorded hidden activations
+    z2, _ = O.linear_fwd(g["hidden"], g["w"], g["b"])
+    np.testing.assert_allclose(z2, z, rtol=1e-4, atol=1e-5)
+
+
+def test_input_pipeline_oracle_matches_torchvision(golden_dir):
+    """oracle.input_pipeline (restatement of Pillow's 8-bit bilinear resample + ToTensor + Normalize) against the real
+    torchvision transform's outputs: uint8 stage and float stage bit for bit."""
+    import hashlib
+    from oracle import input_pipeline as ip
+    g = np.load(os.path.join(golden_dir, "input_pipeline.npz"))
+    for i in range(g["images"].shape[0]):
+        r = ip.resize_bilinear_u8(g["images"][i])
+        assert np.array_equal(r, g["resized_u8"][i])
+        out = ip.transform(g["images"][i], bool(g["flips"][i]))
+        assert np.array_equal(out[:, :16, :], g["first_rows"][i])
+        assert hashlib.sha256(np.ascontiguousarray(out).tobytes()).hexdigest() == str(g["sha256"][i])
+
+
+def test_resize_coeffs_entry_point_matches_oracle():
+    """b200ddp_resize_coeffs is host-only: the C restatement of Resample.c's coefficient set-up equals the oracle's."""
+    import ctypes
+    from b200ddp import _lib
+    from oracle import input_pipeline as ip
+    L = _lib.load()
+    for n_in, n_out in [(32, 224), (32, 32), (17, 224), (48, 96), (1, 8)]:
+        tab = (ctypes.c_int * (5 * n_out))()
+        assert L.b200ddp_resize_coeffs(n_in, n_out, tab) == 0
+        t = np.array(list(tab), np.int32)
+        xm, cnt, co = ip.resample_coeffs(n_in, n_out)
+        assert np.array_equal(t[:n_out], xm) and np.array_equal(t[n_out:2 * n_out], cnt)
+        assert np.array_equal(t[2 * n_out:].reshape(n_out, 3), co[:, :3])
+    tab = (ctypes.c_int * 40)()
+    assert L.b200ddp_resize_coeffs(64, 8, tab) != 0          # reductions are refused, with a message
+    assert b"enlargements" in L.b200ddp_last_error()

@@ -15,9 +15,11 @@ import os as _os
 # Must be in the environment before the first NCCL communicator of the process is created.
 _os.environ.setdefault("NCCL_MAX_NCHANNELS", "16")
 
-from . import _lib, nn, optim  # noqa: F401,E402
+from . import _lib, checkpoint, data, nn, optim  # noqa: F401,E402
 from .arena import FlatArena  # noqa: F401
+from .checkpoint import AsyncCheckpointer, load_checkpoint  # noqa: F401
 from .distributed import DistributedDataParallel  # noqa: F401
+from .evaluate import all_reduce_metrics, evaluate  # noqa: F401
 from .nn import CrossEntropyLoss, SyncBatchNorm  # noqa: F401
 from .optim import Adam  # noqa: F401
 from .sampler import DistributedSampler  # noqa: F401
@@ -38,5 +40,6 @@ def reserve_memory_pool(gigabytes: float = 24.0, device=None) -> None:
     del blk
 
 __all__ = ["reserve_memory_pool", "DistributedDataParallel", "DistributedSampler", "SyncBatchNorm", "convert_sync_batchnorm", "Adam",
-           "CrossEntropyLoss", "FlatArena", "nn", "optim"]
+           "CrossEntropyLoss", "FlatArena", "nn", "optim", "evaluate", "all_reduce_metrics", "data", "checkpoint",
+           "AsyncCheckpointer", "load_checkpoint"]
 __version__ = "0.1.0"

@@ -66,6 +66,15 @@ _PROTOS = {
     "b200ddp_softmax_ce": (c_int, [_P, _P, _P, _P, c_int, c_int, _P, c_int, _P]),
     "b200ddp_conv2d_fwd": (c_int, [_P, _P, c_longlong, _P, _P, _P, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int,
                                    c_int, c_int, c_int, c_int, _P]),
+    "b200ddp_eval_scratch_bytes": (c_longlong, [c_int]),
+    "b200ddp_head_eval": (c_int, [_P, _P, _P, _P, _P, c_int, c_int, c_int, _P, _P, c_longlong, c_int, _P]),
+    "b200ddp_logits_eval": (c_int, [_P, _P, c_int, c_int, _P, _P, c_longlong, c_int, _P]),
+    "b200ddp_resize_coeffs": (c_int, [c_int, c_int, POINTER(c_int)]),
+    "b200ddp_image_transform": (c_int, [_P, _P, _P, c_int, c_int, c_int, c_int, c_int, _P, _P, POINTER(c_float),
+                                        POINTER(c_float), c_int, _P]),
+    "b200ddp_conv2d_fwd_fp32": (c_int, [_P, _P, _P, _P] + [c_int] * 11 + [_P]),
+    "b200ddp_conv2d_dgrad_fp32": (c_int, [_P, _P, _P] + [c_int] * 10 + [_P]),
+    "b200ddp_conv2d_wgrad_fp32": (c_int, [_P, _P, _P] + [c_int] * 10 + [_P]),
     "b200ddp_conv2d_wgrad_workspace_bytes": (c_longlong, [c_int] * 9),
     "b200ddp_conv2d_wgrad": (c_int, [_P, _P, _P, _P, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int,
                                      _P, c_longlong, c_int, _P]),
@@ -164,14 +173,21 @@ def f32c(t, name: str = "tensor"):
 _WORKSPACES: dict = {}
 
 
-def workspace(device, nbytes: int, tag: str = "ws", zero: bool = False):
-    """Per-(device, tag) scratch tensor, grown on demand and reused (the C ABI never allocates)."""
+def workspace(device, nbytes: int, tag: str = "ws", zero: bool = False, stream=None):
+    """Per-(device, tag) scratch tensor, grown on demand and reused (the C ABI never allocates).
+    A tag is used from ONE stream only. `stream` (a torch.cuda.Stream) = that stream when it is not the current one:
+    the buffer is then allocated under it, so that when a larger request replaces the buffer the caching allocator
+    reuses the old block in that stream's order (kernels still reading it there are not overtaken)."""
     key = (str(device), tag)
     buf = _WORKSPACES.get(key)
     if buf is None or buf.numel() < nbytes:
         n = max(int(nbytes), 256)
-        buf = torch.zeros(n, dtype=torch.uint8, device=device) if zero else torch.empty(n, dtype=torch.uint8,
-                                                                                        device=device)
+        make = torch.zeros if zero else torch.empty
+        if stream is not None:
+            with torch.cuda.stream(stream):
+                buf = make(n, dtype=torch.uint8, device=device)
+        else:
+            buf = make(n, dtype=torch.uint8, device=device)
         _WORKSPACES[key] = buf
     return buf
 

@@ -43,6 +43,8 @@ class FlatArena:
         self.m_flat: Optional[torch.Tensor] = None
         self.v_flat: Optional[torch.Tensor] = None
         self.opt_step = 0
+        self._claimed = set()           # parameters whose arena gradient slice was handed out in this backward pass
+        self._claim_reset_queued = False
         self._grad_views: List[torch.Tensor] = []
         with torch.no_grad():
             for i, p in enumerate(self.params):
@@ -64,6 +66,25 @@ class FlatArena:
         """A NEW view tensor over parameter i's gradient slice (fresh object => autograd may adopt it)."""
         o, n = self.offsets[i], self.params[i].numel()
         return self.g_flat[o:o + n].view(self.params[i].shape)
+
+    def claim(self, i: int) -> bool:
+        """First request for parameter i's gradient slice in the running backward pass? (called from backward
+        Functions only; the set is cleared by an end-of-backward engine callback)."""
+        if i in self._claimed:
+            return False
+        self._claimed.add(i)
+        if not self._claim_reset_queued:
+            self._claim_reset_queued = True
+            try:
+                torch.autograd.Variable._execution_engine.queue_callback(self._release_claims)
+            except RuntimeError:        # not inside backward (direct call of a Function's backward in a test)
+                self._claim_reset_queued = False
+                self._claimed.clear()
+        return True
+
+    def _release_claims(self) -> None:
+        self._claimed.clear()
+        self._claim_reset_queued = False
 
     def grad_ptr(self, i: int) -> int:
         return self.g_flat.data_ptr() + 4 * self.offsets[i]

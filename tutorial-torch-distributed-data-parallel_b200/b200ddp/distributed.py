@@ -73,8 +73,8 @@ class DistributedDataParallel(nn.Module):
         self.broadcast_buffers = broadcast_buffers
         self.world_size = dist.get_world_size(process_group) if dist.is_available() and dist.is_initialized() else 1
         self.rank = dist.get_rank(process_group) if self.world_size > 1 else 0
-        self.cuda = self.device.type == "cuda"
-        if self.cuda:
+        self.on_gpu = self.device.type == "cuda"
+        if self.on_gpu:
             _lib.load()           # raises if the extension is missing: no fallback on a GPU
             torch.cuda.set_device(self.device)
             self.comm = get_comm(self.device, process_group)
@@ -95,7 +95,7 @@ class DistributedDataParallel(nn.Module):
             return
         self._verify_shapes()
         with torch.no_grad():
-            if self.cuda:
+            if self.on_gpu:
                 self.comm.broadcast_(self.arena.p_flat, 0)
             else:
                 dist.broadcast(self.arena.p_flat, src=self._src(), group=self.process_group)
@@ -113,7 +113,7 @@ class DistributedDataParallel(nn.Module):
 
     def _broadcast_buffers(self) -> None:
         for b in self.module.buffers():
-            if self.cuda and b.is_floating_point() and b.dtype == torch.float32 and b.is_contiguous():
+            if self.on_gpu and b.is_floating_point() and b.dtype == torch.float32 and b.is_contiguous():
                 self.comm.broadcast_(b, 0)
             else:
                 dist.broadcast(b, src=self._src(), group=self.process_group)

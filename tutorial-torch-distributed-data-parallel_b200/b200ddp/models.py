@@ -11,11 +11,14 @@ several stock layers; the layers they absorb stay in the Sequential as `nn.Ident
   avgpool:    AdaptiveAvgPool2d((6,6)) — the identity at 224x224 input, skipped when the map is already 6x6
   classifier: 0 Dropout*      1 Linear+ReLU+Dropout*  2,3 (fused)  4 Linear+ReLU*  5 (fused)  6 Linear* (head)
 
-(* = b200ddp kernels.) The five convolutions are b200ddp implicit-GEMM tcgen05 kernels too (`conv="b200"`,
-default; conv 6 and 8 fold their ReLU into the epilogue); `conv="cudnn"` keeps torch.nn.Conv2d for A/B runs.
+(* = b200ddp kernels.) Every layer runs b200ddp kernels; `mode` picks their arithmetic for the whole network:
+'tf32' (default) = tcgen05 tensor cores with TF32 operands and fp32 accumulation for convolutions and Linear
+layers — the reference's own convolution numerics (cuDNN TF32); 'fp32' = strict SIMT fp32 everywhere, the parity
+mode of SURVEY 8(d) config 2.
 
 `hidden` scales classifier.1/.4 (BASELINE config 5), `bn=True` builds the AlexNet-BN variant of
-SURVEY 8(d) config 4 (BatchNorm2d after each conv, before its ReLU).
+SURVEY 8(d) config 4 (BatchNorm2d after each conv, before its ReLU); `SyncBatchNorm.convert_sync_batchnorm`
+(README.md:79-81 of the reference) then folds each BN's ReLU into the normalisation kernels.
 """
 from __future__ import annotations
 
@@ -27,43 +30,28 @@ from . import nn as bnn
 
 class AlexNet(nn.Module):
     def __init__(self, num_classes: int = 10, hidden: int = 4096, dropout: float = 0.5, bn: bool = False,
-                 mode="tf32", conv: str = "b200") -> None:
+                 mode="tf32") -> None:
         super().__init__()
         self.bn = bn
-        if conv not in ("b200", "cudnn"):
-            raise ValueError("conv must be 'b200' (own implicit-GEMM kernels) or 'cudnn' (torch.nn.Conv2d)")
-        if not bn and conv == "b200":
+        if not bn:
             self.features = nn.Sequential(
-                bnn.Conv2d(3, 64, kernel_size=11, stride=4, padding=2, pool=True),
+                bnn.Conv2d(3, 64, kernel_size=11, stride=4, padding=2, pool=True, mode=mode),
                 nn.Identity(), nn.Identity(),
-                bnn.Conv2d(64, 192, kernel_size=5, padding=2, pool=True),
+                bnn.Conv2d(64, 192, kernel_size=5, padding=2, pool=True, mode=mode),
                 nn.Identity(), nn.Identity(),
-                bnn.Conv2d(192, 384, kernel_size=3, padding=1, relu=True),
+                bnn.Conv2d(192, 384, kernel_size=3, padding=1, relu=True, mode=mode),
                 nn.Identity(),
-                bnn.Conv2d(384, 256, kernel_size=3, padding=1, relu=True),
+                bnn.Conv2d(384, 256, kernel_size=3, padding=1, relu=True, mode=mode),
                 nn.Identity(),
-                bnn.Conv2d(256, 256, kernel_size=3, padding=1, pool=True),
+                bnn.Conv2d(256, 256, kernel_size=3, padding=1, pool=True, mode=mode),
                 nn.Identity(), nn.Identity(),
-            )
-        elif not bn:
-            self.features = nn.Sequential(
-                nn.Conv2d(3, 64, kernel_size=11, stride=4, padding=2),
-                bnn.ReLUMaxPool2d(), nn.Identity(),
-                nn.Conv2d(64, 192, kernel_size=5, padding=2),
-                bnn.ReLUMaxPool2d(), nn.Identity(),
-                nn.Conv2d(192, 384, kernel_size=3, padding=1),
-                bnn.ReLU(),
-                nn.Conv2d(384, 256, kernel_size=3, padding=1),
-                bnn.ReLU(),
-                nn.Conv2d(256, 256, kernel_size=3, padding=1),
-                bnn.ReLUMaxPool2d(), nn.Identity(),
             )
         else:
             def block(cin, cout, k, s, p, pool):
-                conv_cls = bnn.Conv2d if conv == "b200" else nn.Conv2d
-                layers = [conv_cls(cin, cout, kernel_size=k, stride=s, padding=p), nn.BatchNorm2d(cout), nn.ReLU(inplace=True)]
-                if pool:
-                    layers.append(nn.MaxPool2d(kernel_size=3, stride=2))
+                # conv -> BatchNorm -> ReLU [-> MaxPool(3, 2)]: ReLU and pooling are b200ddp kernels; after
+                # convert_sync_batchnorm the ReLU moves into the SyncBatchNorm kernels (fuse_bn_relu)
+                layers = [bnn.Conv2d(cin, cout, kernel_size=k, stride=s, padding=p, mode=mode), nn.BatchNorm2d(cout)]
+                layers.append(bnn.ReLUMaxPool2d(relu=True) if pool else bnn.ReLU())
                 return layers
             self.features = nn.Sequential(*block(3, 64, 11, 4, 2, True), *block(64, 192, 5, 1, 2, True),
                                           *block(192, 384, 3, 1, 1, False), *block(384, 256, 3, 1, 1, False),
@@ -76,7 +64,9 @@ class AlexNet(nn.Module):
             bnn.Linear(hidden, num_classes, mode=mode),
         )
 
-    def forward(self, x: torch.Tensor) -> torch.Tensor:
+    def forward_hidden(self, x: torch.Tensor) -> torch.Tensor:
+        """Everything up to (not including) the 10-class head: the [B, hidden] input of classifier.6.
+        `b200ddp.evaluate` feeds it to the fused head + metrics kernel."""
         convs = [m for m in self.features if isinstance(m, bnn.Conv2d)]
         if convs and x.is_cuda:
             bnn.prepare_conv_weights(convs, first_needs_dgrad=x.requires_grad)     # all GEMM weight copies, one launch
@@ -84,23 +74,37 @@ class AlexNet(nn.Module):
         if x.shape[-2:] != (6, 6):
             x = self.avgpool(x)
         x = torch.flatten(x, 1)
-        return self.classifier(x)
+        for layer in list(self.classifier)[:-1]:
+            x = layer(x)
+        return x
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        return self.classifier[-1](self.forward_hidden(x))
 
 
-def fuse_bn_relu(model: AlexNet) -> AlexNet:
-    """After convert_sync_batchnorm: fold each `SyncBatchNorm -> ReLU` pair of AlexNet-BN into one kernel."""
-    feats = list(model.features.children())
-    for i, layer in enumerate(feats[:-1]):
-        if isinstance(layer, bnn.SyncBatchNorm) and isinstance(feats[i + 1], nn.ReLU):
-            layer.fuse_relu = True
-            model.features[i + 1] = nn.Identity()
+def fuse_bn_relu(model: nn.Module) -> nn.Module:
+    """Fold the ReLU that follows a SyncBatchNorm into the normalisation kernels, in every nn.Sequential of `model`:
+    `SyncBatchNorm -> ReLU` becomes one fused layer (+ Identity), `SyncBatchNorm -> ReLU+MaxPool` keeps only the
+    pooling in the second layer. Called by `SyncBatchNorm.convert_sync_batchnorm`; idempotent."""
+    for seq in [m for m in model.modules() if isinstance(m, nn.Sequential)]:
+        layers = list(seq.children())
+        for i, layer in enumerate(layers[:-1]):
+            if not isinstance(layer, bnn.SyncBatchNorm) or layer.fuse_relu:
+                continue
+            nxt = layers[i + 1]
+            if isinstance(nxt, (nn.ReLU, bnn.ReLU)):
+                layer.fuse_relu = True
+                seq[i + 1] = nn.Identity()
+            elif isinstance(nxt, bnn.ReLUMaxPool2d) and nxt.relu:
+                layer.fuse_relu = True
+                nxt.relu = False
     return model
 
 
 def load_model(num_classes: int = 10, hidden: int = 4096, seed: int | None = None, mode="tf32", bn: bool = False,
-               dropout: float = 0.5, conv: str = "b200") -> AlexNet:
+               dropout: float = 0.5) -> AlexNet:
     """Counterpart of reference data_and_toy_model.py:41-45. The reference downloads ImageNet weights
     (no network here): weights are torch's default random init, optionally under `seed`."""
     if seed is not None:
         torch.manual_seed(seed)
-    return AlexNet(num_classes=num_classes, hidden=hidden, dropout=dropout, bn=bn, mode=mode, conv=conv)
+    return AlexNet(num_classes=num_classes, hidden=hidden, dropout=dropout, bn=bn, mode=mode)

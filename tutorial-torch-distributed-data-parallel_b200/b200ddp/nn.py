@@ -57,7 +57,8 @@ class _LinearFn(torch.autograd.Function):
         if w.shape[1] != K:
             raise ValueError(f"Linear: input features {K} != weight in_features {w.shape[1]}")
         y = torch.empty((B, N), dtype=torch.float32, device=x.device)
-        need_gate = bool(relu) or p > 0.0
+        # no gate bytes when nothing will be differentiated (evaluate(), reference :136-153: forward under no_grad)
+        need_gate = (bool(relu) or p > 0.0) and any(ctx.needs_input_grad[:3])
         gate = torch.empty((B, N), dtype=torch.uint8, device=x.device) if need_gate else None
         ws_bytes = int(L.b200ddp_linear_workspace_bytes(B, N, K))
         ws = _lib.workspace(x.device, ws_bytes, "linear")
@@ -84,7 +85,7 @@ class _LinearFn(torch.autograd.Function):
         N = w.shape[0]
         dy2 = _lib.f32c(dy.reshape(B, N), "grad_output")
         need_db = ctx.has_bias and ctx.needs_input_grad[2]
-        db = _grad_target(ctx.bias_param, (N,), x2.device) if need_db else None
+        db = _grad_target(ctx.bias_param, (N,), x2.device)[0] if need_db else None
         if gate is not None:
             dz = torch.empty_like(dy2)
             _lib.check(L.b200ddp_gate_bias_bwd(dy2.data_ptr(), gate.data_ptr(), ctx.p, dz.data_ptr(), _lib.ptr(db),
@@ -103,7 +104,7 @@ class _LinearFn(torch.autograd.Function):
             dx = dx.view(ctx.in_shape)
         dw = None
         if ctx.needs_input_grad[1]:
-            dw = _grad_target(ctx.weight_param, (N, K), x2.device)
+            dw = _grad_target(ctx.weight_param, (N, K), x2.device)[0]
             _lib.check(L.b200ddp_linear_bwd_dw(dz.data_ptr(), x2.data_ptr(), dw.data_ptr(),
                                                None if db_done else _lib.ptr(db), B, N, K, ctx.mode, dev, st),
                        "linear_bwd_dw")
@@ -113,13 +114,16 @@ class _LinearFn(torch.autograd.Function):
         return dx, dw, db, None, None, None, None
 
 
-def _grad_target(param, shape, device) -> torch.Tensor:
-    """Where a wgrad kernel should write: straight into the parameter's arena slice when autograd will
-    adopt the tensor as `.grad` (no accumulation pending), else a fresh buffer autograd adds up."""
+def _grad_target(param, shape, device):
+    """Where a wgrad kernel should write, as (tensor, adopted). `adopted` = the tensor is the parameter's own
+    arena slice, which autograd will take over as `.grad`: only when no accumulation is pending (`.grad is None`)
+    AND this is the parameter's first use in the current backward pass (a Parameter used twice in one graph gets
+    the arena view once and a fresh buffer afterwards, so that autograd sums two different tensors instead of
+    counting one aliased tensor twice). Otherwise a fresh buffer that autograd adds up."""
     slot = getattr(param, "_b200_slot", None) if param is not None else None
-    if slot is not None and param.grad is None:
-        return slot[0].grad_view(slot[1])
-    return torch.empty(shape, dtype=torch.float32, device=device)
+    if slot is not None and param.grad is None and slot[0].claim(slot[1]):
+        return slot[0].grad_view(slot[1]), True
+    return torch.empty(shape, dtype=torch.float32, device=device), False
 
 
 class Linear(nn.Linear):
@@ -292,7 +296,7 @@ class _Conv2dFn(torch.autograd.Function):
     produces the bias gradient (sum of the conv output gradient over batch and plane), then wgrad and dgrad."""
 
     @staticmethod
-    def forward(ctx, x, weight, bias, stride, pad, relu, pool, prepared):
+    def forward(ctx, x, weight, bias, stride, pad, relu, pool, prepared, mode):
         L = _lib.load()
         x = _lib.f32c(x, "input")
         w = _lib.f32c(weight, "weight")
@@ -302,7 +306,16 @@ class _Conv2dFn(torch.autograd.Function):
         K = Cin * KH * KW
         ko = _k_order(Cin)
         ctx.dgrad_weights = None
-        if _use_s2d(Cin, KH, KW, stride):
+        ctx.mode = mode
+        if mode == MODE_FP32:
+            # strict mode: direct fp32 convolution on torch's own weight layout (no GEMM copies, no TF32 rounding)
+            N, _, H, W = x.shape
+            OH, OW = (H + 2 * pad - KH) // stride + 1, (W + 2 * pad - KW) // stride + 1
+            y = torch.empty((N, Cout, OH, OW), dtype=torch.float32, device=x.device)
+            _lib.check(L.b200ddp_conv2d_fwd_fp32(x.data_ptr(), w.data_ptr(), _lib.ptr(bias), y.data_ptr(), N, Cin, H, W,
+                                                 Cout, KH, KW, stride, pad, int(bool(relu and not pool)),
+                                                 _lib.dev_index(x), _lib.cur_stream(x.device)), "conv2d_fwd_fp32")
+        elif _use_s2d(Cin, KH, KW, stride):
             # few input channels + stride S (conv1): space-to-depth turns it into a stride-1 ceil(K/S)^2 convolution
             # over 64 channels whose gather reads consecutive pixels; the backward (wgrad) keeps the original x
             y = _conv_forward_s2d(x, w, bias, stride, pad, relu and not pool, prepared)
@@ -326,8 +339,9 @@ class _Conv2dFn(torch.autograd.Function):
                 raise ValueError("Conv2d(pool=True): the convolution output is smaller than the 3x3 pooling window")
             OH, OW = (H - 3) // 2 + 1, (W - 3) // 2 + 1
             out = torch.empty((B, C, OH, OW), dtype=torch.float32, device=x.device)
-            idx = torch.empty((B, C, OH, OW), dtype=torch.uint8, device=x.device)
-            _lib.check(L.b200ddp_relu_maxpool_fwd(y.data_ptr(), out.data_ptr(), idx.data_ptr(), B, C, H, W, int(relu),
+            train = any(ctx.needs_input_grad[:3])          # inference: no argmax codes written or kept
+            idx = torch.empty((B, C, OH, OW), dtype=torch.uint8, device=x.device) if train else None
+            _lib.check(L.b200ddp_relu_maxpool_fwd(y.data_ptr(), out.data_ptr(), _lib.ptr(idx), B, C, H, W, int(relu),
                                                   _lib.dev_index(x), _lib.cur_stream(x.device)), "relu_maxpool_fwd")
             ctx.save_for_backward(x, w, idx)
             return out
@@ -345,7 +359,7 @@ class _Conv2dFn(torch.autograd.Function):
         OH, OW = (H + 2 * pad - KH) // stride + 1, (W + 2 * pad - KW) // stride + 1
         dy = _lib.f32c(dy, "grad_output")
         want_db = ctx.bias_param is not None and ctx.needs_input_grad[2]
-        db = _grad_target(ctx.bias_param, (Cout,), x.device) if want_db else None
+        db = _grad_target(ctx.bias_param, (Cout,), x.device)[0] if want_db else None
         have_db = False
         if want_db and (ctx.pool or ctx.relu):
             nb = int(L.b200ddp_bias_grad_scratch_bytes(N, Cout))
@@ -376,11 +390,22 @@ class _Conv2dFn(torch.autograd.Function):
             _lib.check(L.b200ddp_channel_sum(dz.data_ptr(), db.data_ptr(), N, Cout, OH * OW, scratch.data_ptr(),
                                              scratch.numel(), dev, st), "channel_sum")
         # dgrad first: it is on the critical path and should own the SMs' first wave; wgrad then fills its tail
+        if ctx.mode == MODE_FP32:
+            dx = dw = None
+            if ctx.needs_input_grad[0]:
+                dx = torch.empty_like(x)
+                _lib.check(L.b200ddp_conv2d_dgrad_fp32(dz.data_ptr(), w.data_ptr(), dx.data_ptr(), N, Cin, H, W, Cout, KH,
+                                                       KW, stride, pad, dev, st), "conv2d_dgrad_fp32")
+            if ctx.needs_input_grad[1]:
+                dw = _grad_target(ctx.weight_param, tuple(w.shape), x.device)[0]
+                _lib.check(L.b200ddp_conv2d_wgrad_fp32(x.data_ptr(), dz.data_ptr(), dw.data_ptr(), N, Cin, H, W, Cout, KH,
+                                                       KW, stride, pad, dev, st), "conv2d_wgrad_fp32")
+            return dx, dw, db, None, None, None, None, None, None
         dx = None
         if ctx.needs_input_grad[0]:
             if stride != 1:
                 raise NotImplementedError("b200ddp Conv2d: input gradients are implemented for stride 1 only "
-                                          "(the toy model's strided conv is its first layer)")
+                                          "(the toy model's strided conv is its first layer); mode='fp32' has no such limit")
             ko = _k_order(Cout)          # dgrad reduces over (co, kh', kw')
             if ctx.dgrad_weights is not None:
                 wt, ldt = ctx.dgrad_weights
@@ -389,15 +414,16 @@ class _Conv2dFn(torch.autograd.Function):
             dx = conv2d_forward_raw(dz, wt, ldt, None, Cin, KH, KW, 1, KH - 1 - pad, False, ko)
         dw = None
         if ctx.needs_input_grad[1]:
-            dw = _grad_target(ctx.weight_param, tuple(w.shape), x.device)
+            dw, adopted = _grad_target(ctx.weight_param, tuple(w.shape), x.device)
             ko = _k_order(Cin)
             ktab = _conv_tables(x.device, Cin, H, W, KH, KW) if ko == 0 else None
             nb = int(L.b200ddp_conv2d_wgrad_workspace_bytes(N, Cin, H, W, Cout, KH, KW, stride, pad))
-            ws = _lib.workspace(x.device, max(nb, 256), "conv_wgrad")
             wst = st
             side = None
-            if ctx.needs_input_grad[0] and _overlap_wgrad():
-                # there is a dgrad to overlap with: run wgrad (+ its finalize) on the side stream
+            # The side stream is used only when (a) there is a dgrad to overlap with and (b) the kernel writes the
+            # parameter's own arena slice: a fresh buffer would be summed into `.grad` by autograd on the MAIN stream
+            # (gradient accumulation, no_sync) with nothing ordering that add after the side-stream kernel.
+            if ctx.needs_input_grad[0] and adopted and _overlap_wgrad():
                 side = _side(x.device)
                 main = torch.cuda.current_stream(x.device)
                 ready = torch.cuda.Event()
@@ -406,6 +432,12 @@ class _Conv2dFn(torch.autograd.Function):
                 for t in (x, dz):
                     t.record_stream(side.stream)
                 wst = side.stream.cuda_stream
+                # split-K partials: the two streams never share a workspace (a main-stream wgrad, e.g. the first
+                # layer's, could otherwise overwrite partials a side-stream finalize has not read yet); the side
+                # buffer is allocated under the side stream so the caching allocator orders its reuse there
+                ws = _lib.workspace(x.device, max(nb, 256), "conv_wgrad_side", stream=side.stream)
+            else:
+                ws = _lib.workspace(x.device, max(nb, 256), "conv_wgrad")
             _lib.check(L.b200ddp_conv2d_wgrad(x.data_ptr(), dz.data_ptr(), dw.data_ptr(), _lib.ptr(ktab), ko, N, Cin, H,
                                               W, Cout, KH, KW, stride, pad, ws.data_ptr(), ws.numel(), dev, wst),
                        "conv2d_wgrad")
@@ -416,7 +448,7 @@ class _Conv2dFn(torch.autograd.Function):
                 if not side.callback_queued:
                     side.callback_queued = True
                     torch.autograd.Variable._execution_engine.queue_callback(lambda d=x.device: join_side_work(d))
-        return dx, dw, db, None, None, None, None, None
+        return dx, dw, db, None, None, None, None, None, None
 
 
 class Conv2d(nn.Conv2d):
@@ -424,11 +456,12 @@ class Conv2d(nn.Conv2d):
     following ReLU + MaxPool2d(3, 2) (`pool=True`, alexnet.py:22-24) optionally folded in."""
 
     def __init__(self, in_channels, out_channels, kernel_size, stride=1, padding=0, bias=True, relu=False, pool=False,
-                 device=None, dtype=None) -> None:
+                 mode="tf32", device=None, dtype=None) -> None:
         super().__init__(in_channels, out_channels, kernel_size, stride=stride, padding=padding, bias=bias,
                          device=device, dtype=dtype)
         if self.stride[0] != self.stride[1] or self.padding[0] != self.padding[1]:
             raise ValueError("b200ddp Conv2d needs equal stride / padding in both dimensions")
+        self.mode = _mode_id(mode)                # 'tf32': tcgen05 implicit GEMM (conv.cu); 'fp32': strict SIMT (conv_fp32.cu)
         self.pool = bool(pool)
         self.relu = bool(relu) or self.pool       # the pooled form always includes the ReLU in front of the pool
         self._prepared = None                     # set by prepare_conv_weights(), consumed by the next forward
@@ -473,7 +506,8 @@ class Conv2d(nn.Conv2d):
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         prepared, self._prepared = self._prepared, None
-        return _Conv2dFn.apply(x, self.weight, self.bias, self.stride[0], self.padding[0], self.relu, self.pool, prepared)
+        return _Conv2dFn.apply(x, self.weight, self.bias, self.stride[0], self.padding[0], self.relu, self.pool, prepared,
+                               self.mode)
 
 
 def prepare_conv_weights(convs, first_needs_dgrad: bool = False) -> None:
@@ -486,12 +520,15 @@ def prepare_conv_weights(convs, first_needs_dgrad: bool = False) -> None:
         return
     jobs = []
     for i, conv in enumerate(convs):
-        if not conv.weight.is_cuda or conv.weight.dtype != torch.float32 or not conv.weight.is_contiguous():
+        if (not conv.weight.is_cuda or conv.weight.dtype != torch.float32 or not conv.weight.is_contiguous()
+                or conv.mode == MODE_FP32):
             conv._prepared = None
             continue
         j, prepared = conv._prep_jobs(need_dgrad=torch.is_grad_enabled() and (i > 0 or first_needs_dgrad))
         jobs += j
         conv._prepared = prepared
+    if not jobs:
+        return
     dev = convs[0].weight.device
     for k in range(0, len(jobs), 16):
         part = jobs[k:k + 16]
@@ -518,26 +555,48 @@ class _CrossEntropyFn(torch.autograd.Function):
             raise TypeError("CrossEntropyLoss expects int64 class indices")
         y = labels.contiguous()
         B, C = z.shape
+        _check_label_flag()                 # an out-of-range label seen by an EARLIER call surfaces here
         loss = torch.empty((), dtype=torch.float32, device=z.device)
-        dlogits = torch.empty_like(z)
-        _lib.check(L.b200ddp_softmax_ce(z.data_ptr(), y.data_ptr(), loss.data_ptr(), dlogits.data_ptr(), B, C, None,
-                                        dev, _lib.cur_stream(z.device)), "softmax_ce")
-        ctx.save_for_backward(dlogits)
+        dlogits = torch.empty_like(z) if ctx.needs_input_grad[0] else None      # evaluate(): loss only
+        _lib.check(L.b200ddp_softmax_ce(z.data_ptr(), y.data_ptr(), loss.data_ptr(), _lib.ptr(dlogits), B, C,
+                                        _label_flag().data_ptr(), dev, _lib.cur_stream(z.device)), "softmax_ce")
+        if dlogits is not None:
+            ctx.save_for_backward(dlogits)
         return loss
 
     @staticmethod
     def backward(ctx, gout):
         (dlogits,) = ctx.saved_tensors
         L = _lib.load()
+        _check_label_flag()
         g = gout.to(torch.float32).reshape(1).contiguous()
-        out = dlogits.clone() if dlogits.data_ptr() % 16 else dlogits
+        out = dlogits.clone()               # the saved tensor stays intact (retain_graph / a second backward)
         _lib.check(L.b200ddp_scale_by_device_scalar(out.data_ptr(), out.numel(), g.data_ptr(), 0,
                                                     _lib.dev_index(out), _lib.cur_stream(out.device)), "ce_bwd")
         return out, None
 
 
+_LABEL_FLAG = []
+
+
+def _label_flag() -> torch.Tensor:
+    """One int32 in pinned (device-mapped) host memory that softmax_ce raises for a label outside [0, C): the host
+    reads it without synchronising, so the report arrives asynchronously - like stock torch's device assert - at the
+    next loss / backward call that runs after the kernel has executed."""
+    if not _LABEL_FLAG:
+        _LABEL_FLAG.append(torch.zeros(1, dtype=torch.int32).pin_memory())
+    return _LABEL_FLAG[0]
+
+
+def _check_label_flag() -> None:
+    if _LABEL_FLAG and int(_LABEL_FLAG[0][0]) != 0:
+        _LABEL_FLAG[0][0] = 0
+        raise _lib.B200Error("CrossEntropyLoss: a class index outside [0, n_classes) other than ignore_index=-100 "
+                             "was passed in an earlier call (that row was given zero loss and zero gradient)")
+
+
 class CrossEntropyLoss(nn.Module):
-    """Mean softmax cross-entropy over the batch (nn.CrossEntropyLoss() defaults, reference :248)."""
+    """Mean softmax cross-entropy over the batch (nn.CrossEntropyLoss() defaults incl. ignore_index=-100, reference :248)."""
 
     def forward(self, logits: torch.Tensor, labels: torch.Tensor) -> torch.Tensor:
         return _CrossEntropyFn.apply(logits, labels)
@@ -554,8 +613,8 @@ class _ReluMaxPoolFn(torch.autograd.Function):
         B, C, H, W = x.shape
         OH, OW = (H - 3) // 2 + 1, (W - 3) // 2 + 1
         y = torch.empty((B, C, OH, OW), dtype=torch.float32, device=x.device)
-        idx = torch.empty((B, C, OH, OW), dtype=torch.uint8, device=x.device)
-        _lib.check(L.b200ddp_relu_maxpool_fwd(x.data_ptr(), y.data_ptr(), idx.data_ptr(), B, C, H, W, int(relu),
+        idx = torch.empty((B, C, OH, OW), dtype=torch.uint8, device=x.device) if ctx.needs_input_grad[0] else None
+        _lib.check(L.b200ddp_relu_maxpool_fwd(x.data_ptr(), y.data_ptr(), _lib.ptr(idx), B, C, H, W, int(relu),
                                               _lib.dev_index(x), _lib.cur_stream(x.device)), "relu_maxpool_fwd")
         ctx.save_for_backward(idx)
         ctx.in_shape = (B, C, H, W)
@@ -707,8 +766,8 @@ class _SyncBatchNormFn(torch.autograd.Function):
         scratch_bytes = int(L.b200ddp_bn_scratch_bytes(B, C))
         scratch = _lib.workspace(x.device, scratch_bytes, "bn", zero=True)
         sums = torch.empty(2 * C, dtype=torch.float32, device=x.device)   # sum_dy | sum_dy_xmu
-        gw = _grad_target(ctx.weight_param, (C,), x.device) if weight is not None and ctx.needs_input_grad[1] else None
-        gb = _grad_target(ctx.bias_param, (C,), x.device) if ctx.bias_param is not None and ctx.needs_input_grad[2] else None
+        gw = _grad_target(ctx.weight_param, (C,), x.device)[0] if weight is not None and ctx.needs_input_grad[1] else None
+        gb = _grad_target(ctx.bias_param, (C,), x.device)[0] if ctx.bias_param is not None and ctx.needs_input_grad[2] else None
         _lib.check(L.b200ddp_bn_bwd_reduce(dy.data_ptr(), x.data_ptr(), _lib.ptr(y_relu), mean.data_ptr(),
                                            invstd.data_ptr(), B, C, HW, sums.data_ptr(), sums.data_ptr() + 4 * C,
                                            _lib.ptr(gw), _lib.ptr(gb), scratch.data_ptr(), scratch.numel(), dev, st),
@@ -782,7 +841,14 @@ class SyncBatchNorm(_BatchNorm):
 
     @classmethod
     def convert_sync_batchnorm(cls, module: nn.Module, process_group=None) -> nn.Module:
-        """Recursively replace every BatchNorm*D child by SyncBatchNorm, sharing parameters and buffers."""
+        """Recursively replace every BatchNorm*D child by SyncBatchNorm, sharing parameters and buffers
+        (torch batchnorm.py:844-905), then fold each `SyncBatchNorm -> ReLU` pair of a Sequential into the
+        normalisation kernels (models.fuse_bn_relu) so that no eager activation remains between them."""
+        from .models import fuse_bn_relu
+        return fuse_bn_relu(cls._convert(module, process_group))
+
+    @classmethod
+    def _convert(cls, module: nn.Module, process_group=None) -> nn.Module:
         out = module
         if isinstance(module, _BatchNorm) and not isinstance(module, SyncBatchNorm):
             out = cls(module.num_features, module.eps, module.momentum, module.affine, module.track_running_stats,
@@ -798,6 +864,6 @@ class SyncBatchNorm(_BatchNorm):
             if hasattr(module, "qconfig"):
                 out.qconfig = module.qconfig
         for name, child in module.named_children():
-            out.add_module(name, cls.convert_sync_batchnorm(child, process_group))
+            out.add_module(name, cls._convert(child, process_group))
         del module
         return out

@@ -76,7 +76,7 @@ class Reducer:
             raise ValueError("nonfinite must be 'propagate' or 'zero'")
         self.arena = arena
         self.pg = process_group
-        self.cuda = arena.device.type == "cuda"
+        self.on_gpu = arena.device.type == "cuda"
         self.world = dist.get_world_size(process_group) if dist.is_available() and dist.is_initialized() else 1
         self.comm = comm
         self.clip_value = None if clip_grad_value is None else float(clip_grad_value)
@@ -95,7 +95,7 @@ class Reducer:
         params = arena.params
         sizes = [p.numel() * 4 for p in params]
         caps = [int(first_bucket_cap_mb * MiB), int(bucket_cap_mb * MiB)]
-        if self.cuda or _lib_available():
+        if self.on_gpu or _lib_available():
             groups = plan_buckets(sizes, caps)
         else:  # pragma: no cover - only when the .so has not been built on a CPU-only box
             raise _lib.B200Error("libb200ddp.so is required for the bucket planner")
@@ -120,7 +120,7 @@ class Reducer:
         self._tail_prefix = None           # (bucket index, set of prefix members, prefix end offset)
         self._tail_prefix_pending = 0
         self._tail_early = False
-        if (self.cuda and self.world > 1 and self.clip_value is None and self.clip_norm is None and self.buckets
+        if (self.on_gpu and self.world > 1 and self.clip_value is None and self.clip_norm is None and self.buckets
                 and os.environ.get("B200DDP_TAIL_SPLIT", "1") != "0"):
             last = self.buckets[-1]
             if len(last.members) > 2:
@@ -128,7 +128,7 @@ class Reducer:
                 p_start, p_end = arena.span(prefix[0], prefix[-1])
                 if (p_end - p_start) * 4 >= (1 << 20):
                     self._tail_prefix = (last.index, frozenset(prefix), p_end)
-        if self.cuda:
+        if self.on_gpu:
             dev = arena.device
             self._sq = torch.zeros(1, dtype=torch.float32, device=dev)
             self._coef = torch.ones(1, dtype=torch.float32, device=dev)
@@ -173,7 +173,7 @@ class Reducer:
         if not self._callback_queued:
             self._reset()
             self._callback_queued = True
-            if self.cuda and self.clip_norm is not None:
+            if self.on_gpu and self.clip_norm is not None:
                 self._sq.zero_()
             Variable._execution_engine.queue_callback(self._finalize)
         self._ready_order.append(i)
@@ -182,7 +182,7 @@ class Reducer:
             # gradient was produced outside the arena (e.g. by a cuDNN wgrad): pack it into its slice
             g = param.grad
             view = arena.grad_view(i)
-            if self.cuda:
+            if self.on_gpu:
                 L = _lib.load()
                 src = g if g.is_contiguous() else g.contiguous()
                 _lib.check(L.b200ddp_pack_scale_clip(view.data_ptr(), src.data_ptr(), src.numel(), 1.0, 0.0, 0,
@@ -215,7 +215,7 @@ class Reducer:
     def _bucket_ready(self, b: _Bucket) -> None:
         t = self._bucket_tensor(b)
         n = b.end - b.start
-        if self.cuda:
+        if self.on_gpu:
             from .nn import join_side_work
             join_side_work(t.device)       # weight gradients computed on the side stream must be complete
             L = _lib.load()
@@ -242,7 +242,7 @@ class Reducer:
         if self.world == 1:
             return
         t = self._bucket_tensor(b)
-        if self.cuda:
+        if self.on_gpu:
             premul = 1.0 if self.pass_prescaled else 1.0 / self.world
             if self._tail_early and self._tail_prefix is not None and b.index == self._tail_prefix[0]:
                 t = self.arena.g_flat[self._tail_prefix[2]:b.end]      # the prefix is already being reduced
@@ -265,7 +265,7 @@ class Reducer:
             if self.clip_norm is not None:
                 self._clip_by_norm_then_reduce()
             if self.world > 1:
-                if self.cuda:
+                if self.on_gpu:
                     self.comm.bucket_reduce_join(self.arena.device)
                 else:
                     for b in self.buckets:
@@ -276,7 +276,7 @@ class Reducer:
 
     def _clip_by_norm_then_reduce(self) -> None:
         g = self.arena.g_flat
-        if self.cuda:
+        if self.on_gpu:
             L = _lib.load()
             dev, st = _lib.dev_index(g), _lib.cur_stream(g.device)
             _lib.check(L.b200ddp_clip_coef(self._sq.data_ptr(), self.clip_norm, 1 if self.nonfinite_zero else 0,

@@ -10,7 +10,18 @@ namespace b200 {
 
 static thread_local char g_err[1024] = "";
 std::atomic<unsigned long long> g_launches{0};
-std::atomic<int> g_sm_budget{kNumSMs};
+std::atomic<int> g_sm_budget{0};          // 0 = all SMs of the current device
+
+int num_sms() {
+  static std::atomic<int> cache[64];
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return kNumSMs;
+  int n = cache[dev & 63].load(std::memory_order_relaxed);
+  if (n > 0) return n;
+  if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) return kNumSMs;
+  cache[dev & 63].store(n, std::memory_order_relaxed);
+  return n;
+}
 
 void set_error(const char* fmt, ...) {
   va_list ap;
@@ -30,9 +41,9 @@ int b200ddp_version(void) { return 100; }
 unsigned long long b200ddp_launch_count(void) { return b200::g_launches.load(); }
 
 int b200ddp_set_sm_budget(int sms) {
-  const int prev = b200::g_sm_budget.load();
-  if (sms <= 0 || sms > b200::kNumSMs) sms = b200::kNumSMs;
-  if (sms < 16) sms = 16;
+  const int prev = b200::sm_budget();
+  if (sms <= 0) sms = 0;                   // all SMs of whichever device a call runs on
+  else if (sms < 16) sms = 16;
   b200::g_sm_budget.store(sms);
   return prev;
 }

@@ -94,7 +94,7 @@ extern "C" int b200ddp_adam_step_flat(float* p, const float* g, float* m, float*
   const long long n4 = n >> 2;
   long long want = (n4 + 255) / 256;
   if (want < 1) want = 1;
-  const long long cap = (long long)kNumSMs * 8;
+  const long long cap = (long long)num_sms() * 8;
   const int grid = (int)(want < cap ? want : cap);
   adam_flat_kernel<<<grid, 256, 0, as_stream(stream)>>>(p, g, m, v, n, s, grad_scale_dev);
   B200_LAUNCH_OK();

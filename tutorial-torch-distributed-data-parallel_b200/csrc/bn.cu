@@ -229,7 +229,7 @@ int b200ddp_bn_elemt(const float* x, const float* mean, const float* invstd, con
   B200_CHECK_ARG(x && mean && invstd && y && B > 0 && C > 0 && HW > 0, "bn_elemt: bad argument");
   B200_DEVICE(device);
   const long long planes = (long long)B * C;
-  const int grid = (int)(planes < kNumSMs * 8 ? planes : kNumSMs * 8);
+  const int grid = (int)(planes < num_sms() * 8 ? planes : num_sms() * 8);
   bn_elemt_kernel<<<grid, 256, 0, as_stream(stream)>>>(x, mean, invstd, weight, bias, y, planes, C, HW, relu);
   B200_LAUNCH_OK();
   return 0;
@@ -261,7 +261,7 @@ int b200ddp_bn_bwd_elemt(const float* dy, const float* x, const float* y_relu, c
                  "bn_bwd_elemt: bad argument");
   B200_DEVICE(device);
   const long long planes = (long long)B * C;
-  const int grid = (int)(planes < kNumSMs * 8 ? planes : kNumSMs * 8);
+  const int grid = (int)(planes < num_sms() * 8 ? planes : num_sms() * 8);
   bn_bwd_elemt_kernel<<<grid, 256, 0, as_stream(stream)>>>(dy, x, y_relu, mean, invstd, weight, sum_dy, sum_dy_xmu,
                                                            inv_count, dx, planes, C, HW);
   B200_LAUNCH_OK();

@@ -16,7 +16,8 @@
 
 namespace b200 {
 
-constexpr int kNumSMs = 148;  // B200: 2 dies x 74 SMs
+constexpr int kNumSMs = 148;  // B200: 2 dies x 74 SMs. Sizes fixed-size scratch layouts only; launch grids use num_sms()
+int num_sms();                // SM count of the CURRENT device (cudaDevAttrMultiProcessorCount, cached per device)
 
 // Error codes. CUDA runtime errors are offset so they stay disjoint from NCCL ones.
 enum : int {
@@ -32,7 +33,10 @@ void set_error(const char* fmt, ...);
 extern std::atomic<unsigned long long> g_launches;
 // SMs the grid planners may count on (b200ddp_set_sm_budget): all 148 unless a resident collective owns some.
 extern std::atomic<int> g_sm_budget;
-inline int sm_budget() { return g_sm_budget.load(std::memory_order_relaxed); }
+inline int sm_budget() {
+  const int b = g_sm_budget.load(std::memory_order_relaxed), n = num_sms();
+  return (b <= 0 || b > n) ? n : b;       // 0 = every SM of the device
+}
 
 inline void count_launch(int n = 1) { g_launches.fetch_add((unsigned long long)n, std::memory_order_relaxed); }
 
@@ -90,6 +94,20 @@ struct DeviceGuard {
   }
 
 inline cudaStream_t as_stream(void* s) { return reinterpret_cast<cudaStream_t>(s); }
+
+// cudaFuncAttributeMaxDynamicSharedMemorySize is a PER-DEVICE attribute of a kernel: remember, per device ordinal,
+// whether it has been raised (one bit per device in `done_mask`, one mask per kernel instantiation).
+template <typename F>
+inline cudaError_t ensure_max_dyn_smem(F* func, std::atomic<unsigned long long>& done_mask, int bytes = 227 * 1024) {
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  const unsigned long long bit = 1ull << (dev & 63);
+  if (done_mask.load(std::memory_order_acquire) & bit) return cudaSuccess;
+  e = cudaFuncSetAttribute(func, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+  if (e == cudaSuccess) done_mask.fetch_or(bit, std::memory_order_release);
+  return e;
+}
 
 inline int ceil_div(long long a, long long b) { return (int)((a + b - 1) / b); }
 

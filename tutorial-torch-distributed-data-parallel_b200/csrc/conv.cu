@@ -745,14 +745,13 @@ template <int BN, int PL, bool TWO = false, int KS = 1>
 int launch_fwd(const CUtensorMap& tmW, const ConvFwdParams& p, cudaStream_t stream) {
   const size_t stage_bytes = (size_t)BN * CBK * 4 * KS;  // weight tiles only: the im2col tile lives in TMEM
   const size_t smem = 1024 + (size_t)p.stages * stage_bytes + (2 * p.stages + 1) * 8 + 16;
-  static bool attr_set = false;
-  if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(conv_fwd_kernel<BN, PL, TWO, KS>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+  static std::atomic<unsigned long long> attr_devices{0};
+  {
+    cudaError_t e = ensure_max_dyn_smem(conv_fwd_kernel<BN, PL, TWO, KS>, attr_devices);
     if (e != cudaSuccess) {
       set_error("cudaFuncSetAttribute(conv_fwd_kernel<%d>) -> %s", BN, cudaGetErrorString(e));
       return kCudaErrBase + (int)e;
     }
-    attr_set = true;
   }
   dim3 grid((p.M + CBM - 1) / CBM, (p.Cout + BN - 1) / BN, 1);
   conv_fwd_kernel<BN, PL, TWO, KS><<<grid, FwdShape<TWO>::kThreads, smem, stream>>>(tmW, p);
@@ -769,14 +768,13 @@ template <int BN, int PL, int R>
 int launch_wgrad(const ConvWgradParams& p, cudaStream_t stream) {
   const size_t stage_bytes = (size_t)(CBM * R + BN) * CBK * 4;
   const size_t smem = 1024 + (size_t)p.stages * stage_bytes + (2 * p.stages + 1) * 8 + 32 + (size_t)CBM * R * 8;
-  static bool attr_set = false;
-  if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(conv_wgrad_kernel<BN, PL, R>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+  static std::atomic<unsigned long long> attr_devices{0};
+  {
+    cudaError_t e = ensure_max_dyn_smem(conv_wgrad_kernel<BN, PL, R>, attr_devices);
     if (e != cudaSuccess) {
       set_error("cudaFuncSetAttribute(conv_wgrad_kernel<%d,%d,%d>) -> %s", BN, PL, R, cudaGetErrorString(e));
       return kCudaErrBase + (int)e;
     }
-    attr_set = true;
   }
   dim3 grid((p.K + CBM * R - 1) / (CBM * R), (p.Cout + BN - 1) / BN, p.splits);
   conv_wgrad_kernel<BN, PL, R><<<grid, kWgThreads, smem, stream>>>(p);
@@ -982,7 +980,7 @@ int b200ddp_conv2d_wgrad(const float* x, const float* dy, float* dw, const int* 
       const long long total = (long long)Cout * K;
       B200_CHECK_ARG(total < (1LL << 31), "conv2d_wgrad: weight tensor too large");
       long long want = (total / 4 + 255) / 256;
-      const int grid = (int)(want < kNumSMs * 16 ? want : kNumSMs * 16);
+      const int grid = (int)(want < num_sms() * 16 ? want : num_sms() * 16);
       wgrad_finalize_ci_kernel<<<grid, 256, 0, s>>>(reinterpret_cast<const float*>(ws), w.splits, Cout, Cin, KH * KW, dw);
       B200_LAUNCH_OK();
       return 0;
@@ -1028,7 +1026,7 @@ int b200ddp_conv2d_weight_prep(const float* w, float* out, int Cout, int Cin, in
   B200_DEVICE(device);
   const long long total = prep_total(Cout, Cin, KH, KW, ld_out, mode);
   long long want = (total + 255) / 256;
-  const int grid = (int)(want < kNumSMs * 8 ? (want < 1 ? 1 : want) : kNumSMs * 8);
+  const int grid = (int)(want < num_sms() * 8 ? (want < 1 ? 1 : want) : num_sms() * 8);
   conv_weight_prep_kernel<<<grid, 256, 0, as_stream(stream)>>>(w, out, Cout, Cin, KH, KW, ld_out, mode);
   B200_LAUNCH_OK();
   return 0;
@@ -1048,7 +1046,7 @@ int b200ddp_conv2d_weight_prep_multi(const b200ddp_weight_prep_job* jobs, int nj
     const long long total = prep_total(q.Cout, q.Cin, q.KH, q.KW, q.ld_out, q.mode);
     long long want = (total + 1023) / 1024;                      // ~4 elements per thread
     if (want < 1) want = 1;
-    if (want > kNumSMs * 4) want = kNumSMs * 4;
+    if (want > num_sms() * 4) want = num_sms() * 4;
     J.job[j] = q;
     J.first_block[j] = blocks;
     blocks += (int)want;

@@ -209,14 +209,13 @@ template <int BN, bool EPI, int RS>
 int launch_bn(const CUtensorMap& tmA, const CUtensorMap& tmB, const KParams& p, cudaStream_t stream) {
   const size_t stage_bytes = (size_t)(BM * RS + BN) * BK * 4;
   const size_t smem = 1024 + (size_t)p.stages * stage_bytes + (2 * p.stages + 1) * 8 + 16;
-  static bool attr_set = false;   // per template instance; benign race (idempotent)
-  if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(tf32_gemm_kernel<BN, EPI, RS>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+  static std::atomic<unsigned long long> attr_devices{0};   // per template instance, one bit per device
+  {
+    cudaError_t e = ensure_max_dyn_smem(tf32_gemm_kernel<BN, EPI, RS>, attr_devices);
     if (e != cudaSuccess) {
       set_error("cudaFuncSetAttribute(tf32_gemm_kernel) -> %s", cudaGetErrorString(e));
       return kCudaErrBase + (int)e;
     }
-    attr_set = true;
   }
   dim3 grid((p.M + BM * RS - 1) / (BM * RS), (p.N + BN - 1) / BN, p.splits);
   tf32_gemm_kernel<BN, EPI, RS><<<grid, kThreads, smem, stream>>>(tmA, tmB, p);

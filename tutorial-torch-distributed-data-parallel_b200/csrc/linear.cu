@@ -206,12 +206,12 @@ int splitk_finalize_launch(const float* ws, int splits, int rows, int cols, floa
   const bool vec = (cols & 3) == 0 && (ldo & 3) == 0 && total < (1LL << 31) && (((uintptr_t)ws | (uintptr_t)out) & 15) == 0;
   if (vec) {
     long long want = (total / 4 + 255) / 256;
-    const long long cap = (long long)kNumSMs * 16;
+    const long long cap = (long long)num_sms() * 16;
     const int grid = (int)(want < cap ? (want < 1 ? 1 : want) : cap);
     splitk_finalize_vec4_kernel<<<grid, 256, 0, stream>>>(ws, splits, rows, cols, out, ldo, ep);
   } else {
     long long want = (total + 255) / 256;
-    const long long cap = (long long)kNumSMs * 8;
+    const long long cap = (long long)num_sms() * 8;
     const int grid = (int)(want < cap ? (want < 1 ? 1 : want) : cap);
     splitk_finalize_kernel<<<grid, 256, 0, stream>>>(ws, splits, rows, cols, out, ldo, ep);
   }
@@ -454,7 +454,7 @@ int b200ddp_linear_bwd_dx(const float* dz, const float* w, float* dx, int B, int
   if (N <= kSmallN) {
     const long long total = (long long)B * K;
     long long want = (total + 255) / 256;
-    const int grid = (int)(want < kNumSMs * 8 ? want : kNumSMs * 8);
+    const int grid = (int)(want < num_sms() * 8 ? want : num_sms() * 8);
     linear_smalln_dx_kernel<<<grid, 256, 0, s>>>(dz, w, dx, B, N, K);
     B200_LAUNCH_OK();
     return 0;

@@ -10,18 +10,31 @@
 
 namespace b200 {
 
+constexpr long long kIgnoreIndex = -100;   // nn.CrossEntropyLoss(ignore_index=-100) default
+
+// Rows whose label equals ignore_index contribute nothing and are left out of the mean (torch semantics);
+// any other label outside [0, C) is an error: the row is treated as ignored (zero gradient row, never
+// uninitialised memory) and *err_flag is raised for the host to report.
 __global__ void __launch_bounds__(1024) softmax_ce_kernel(const float* __restrict__ logits,
                                                           const long long* __restrict__ labels,
                                                           float* __restrict__ loss, float* __restrict__ dlogits,
                                                           int B, int C, int* __restrict__ err_flag) {
   __shared__ float red[32];
+  float cnt = 0.f;
+  for (int b = threadIdx.x; b < B; b += blockDim.x) {
+    const long long y = labels[b];
+    if (y >= 0 && y < C) cnt += 1.f;
+    else if (y != kIgnoreIndex && err_flag) atomicExch(err_flag, 1);
+  }
+  const float nvalid = block_sum<float>(cnt, red);          // exact: B < 2^24
+  const float inv = nvalid > 0.f ? 1.0f / nvalid : 0.f;
   float local = 0.f;
-  const float invB = 1.0f / (float)B;
   for (int b = threadIdx.x; b < B; b += blockDim.x) {
     const float* z = logits + (long long)b * C;
     const long long y = labels[b];
     if (y < 0 || y >= C) {
-      if (err_flag) atomicExch(err_flag, 1);
+      if (dlogits)
+        for (int c = 0; c < C; ++c) dlogits[(long long)b * C + c] = 0.f;
       continue;
     }
     float mx = -INFINITY;
@@ -34,12 +47,12 @@ __global__ void __launch_bounds__(1024) softmax_ce_kernel(const float* __restric
       float* d = dlogits + (long long)b * C;
       for (int c = 0; c < C; ++c) {
         const float sm = expf(z[c] - mx - lse);
-        d[c] = (sm - (c == (int)y ? 1.f : 0.f)) * invB;
+        d[c] = (sm - (c == (int)y ? 1.f : 0.f)) * inv;
       }
     }
   }
   const float tot = block_sum<float>(local, red);
-  if (threadIdx.x == 0) loss[0] = tot * invB;
+  if (threadIdx.x == 0) loss[0] = nvalid > 0.f ? tot * inv : __int_as_float(0x7fc00000);   // all ignored: nan, as torch
 }
 
 }  // namespace b200

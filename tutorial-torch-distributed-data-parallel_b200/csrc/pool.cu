@@ -40,7 +40,7 @@ __global__ void __launch_bounds__(256) relu_maxpool_fwd_kernel(const float* __re
   const int ohw = OH * OW, hw = H * W, n = np * ohw;
   const float* xb = x + pl0 * hw;
   float* yb = y + pl0 * ohw;
-  unsigned char* ib = idx + pl0 * ohw;
+  unsigned char* ib = idx ? idx + pl0 * ohw : nullptr;    // null in inference: the argmax codes are not needed
   Walk3 wk(threadIdx.x, blockDim.x, OH, OW);
   for (int i = threadIdx.x; i < n; i += blockDim.x, wk.next()) {
     const float* xp = xb + wk.pl * hw + (wk.r * kPoolS) * W + wk.c * kPoolS;
@@ -59,7 +59,7 @@ __global__ void __launch_bounds__(256) relu_maxpool_fwd_kernel(const float* __re
     unsigned char code = (unsigned char)bi;
     if (relu && !(best > 0.f)) { best = 0.f; code = 255; }
     yb[i] = best;
-    ib[i] = code;
+    if (ib) ib[i] = code;
   }
 }
 
@@ -224,7 +224,7 @@ __global__ void __launch_bounds__(256) dropout_fwd_kernel(const float* __restric
 static inline int ew_grid(long long n) {
   long long want = (n + 255) / 256;
   if (want < 1) want = 1;
-  const long long cap = (long long)kNumSMs * 16;
+  const long long cap = (long long)num_sms() * 16;
   return (int)(want < cap ? want : cap);
 }
 
@@ -236,7 +236,7 @@ extern "C" {
 
 int b200ddp_relu_maxpool_fwd(const float* x, float* y, unsigned char* idx, int B, int C, int H, int W, int relu,
                              int device, void* stream) {
-  B200_CHECK_ARG(x && y && idx && B > 0 && C > 0 && H >= 3 && W >= 3, "relu_maxpool_fwd: bad argument");
+  B200_CHECK_ARG(x && y && B > 0 && C > 0 && H >= 3 && W >= 3, "relu_maxpool_fwd: bad argument");
   B200_DEVICE(device);
   const int OH = (H - kPoolK) / kPoolS + 1, OW = (W - kPoolK) / kPoolS + 1;
   const long long planes = (long long)B * C;
@@ -267,7 +267,7 @@ static int pool_bwd_launch(const float* dy, const unsigned char* idx, float* dx,
   }
   B200_DEVICE(device);
   const long long planes = (long long)B * C, nchunks = (planes + P - 1) / P;
-  const int grid = (int)(nchunks < (long long)kNumSMs * 8 ? nchunks : (long long)kNumSMs * 8);
+  const int grid = (int)(nchunks < (long long)num_sms() * 8 ? nchunks : (long long)num_sms() * 8);
   relu_maxpool_bwd_kernel<<<grid, 256, 0, as_stream(stream)>>>(dy, idx, dx, plane_sums, B, C, H, W, OH, OW, P);
   B200_LAUNCH_OK();
   if (db) {
@@ -299,7 +299,7 @@ int b200ddp_relu_bwd_bias(const float* dy, const float* y, float* dx, float* db,
   B200_DEVICE(device);
   const long long planes = (long long)B * C;
   const long long want = (planes + 7) / 8;                 // 8 warps per CTA, one plane per warp and pass
-  const int grid = (int)(want < (long long)kNumSMs * 16 ? want : (long long)kNumSMs * 16);
+  const int grid = (int)(want < (long long)num_sms() * 16 ? want : (long long)num_sms() * 16);
   double* plane_sums = reinterpret_cast<double*>(scratch);
   relu_bwd_bias_kernel<<<grid, 256, 0, as_stream(stream)>>>(dy, y, dx, plane_sums, planes, HW);
   B200_LAUNCH_OK();

@@ -16,7 +16,7 @@ constexpr int kRedMaxBlocks = kNumSMs * 4;  // 592 partials at most
 static inline int stream_grid(long long n) {
   long long want = ((n >> 2) + kRedThreads - 1) / kRedThreads;
   if (want < 1) want = 1;
-  const long long cap = (long long)kNumSMs * 8;
+  const long long cap = (long long)num_sms() * 8;
   return (int)(want < cap ? want : cap);
 }
 
