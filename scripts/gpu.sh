@@ -1,0 +1,47 @@
+#!/bin/bash
+# The gpurun command lines of this repo, in one place:  gpurun [--gpus N] --timeout T -- 'bash scripts/gpu.sh <what> [args]'
+# Everything lands in gpurun_out/ (scratch); summaries worth keeping are copied to profiles/ by hand.
+#   tests [pytest args]  GPU parity tests on one GPU (not multigpu), then smoke()
+#   multi N              multigpu tests (2 ranks) + bench.py at N ranks
+#   bench [args]         bench.py with the given arguments
+#   launches             ncu launch list of a 3-step bench (after the same command ran clean without ncu)
+#   ncu REGEX N [args]   ncu --set full of the kernels matching REGEX (N launches) from scripts/kernel_bench.py
+#   kbench [args]        scripts/kernel_bench.py
+mkdir -p gpurun_out
+export PYTHONUNBUFFERED=1
+what=$1; shift
+T="timeout 1500 python -m pytest -q -p no:cacheprovider --timeout 900"
+case "$what" in
+  tests)
+    nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,power.draw --format=csv > gpurun_out/gpu.txt 2>&1
+    $T tests -m "gpu and not multigpu" "$@" > gpurun_out/t_gpu.log 2>&1; echo "tests rc=$?"
+    tail -n 40 gpurun_out/t_gpu.log
+    timeout 300 python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/smoke.log 2>&1; echo "smoke rc=$?"; tail -n 2 gpurun_out/smoke.log
+    ;;
+  multi)
+    n=${1:-2}
+    $T tests -m "multigpu" > gpurun_out/t_multi.log 2>&1; echo "multi tests rc=$?"; tail -n 25 gpurun_out/t_multi.log
+    timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port 29511 \
+      bench.py --gpus $n --steps 50 --warmup 5 > gpurun_out/bench_n$n.log 2>gpurun_out/bench_n$n.err; echo "bench n=$n rc=$?"
+    grep -h '^{' gpurun_out/bench_n$n.log | cut -c1-4000; tail -n 8 gpurun_out/bench_n$n.err
+    ;;
+  bench)
+    timeout 900 python bench.py "$@" > gpurun_out/bench.log 2>gpurun_out/bench.err; echo "bench rc=$?"
+    grep -h '^{' gpurun_out/bench.log | cut -c1-6000; tail -n 8 gpurun_out/bench.err
+    ;;
+  launches)
+    timeout 300 python bench.py --steps 3 --warmup 3 --no-extras > gpurun_out/bench_short.log 2>&1 && \
+    timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 3000 --csv --log-file gpurun_out/launches.csv \
+       python bench.py --steps 3 --warmup 3 --no-extras > gpurun_out/ncu_bench.log 2>&1; echo "ncu list rc=$?"
+    ;;
+  ncu)
+    regex=$1; count=${2:-8}; shift 2
+    timeout 300 python scripts/kernel_bench.py --prof "$@" > gpurun_out/prof_plain.log 2>&1 && \
+    timeout 1200 ncu --set full --clock-control none --import-source on -k regex:$regex -c $count -o gpurun_out/prof_$regex -f \
+       python scripts/kernel_bench.py --prof "$@" > gpurun_out/ncu_$regex.log 2>&1; echo "ncu rc=$?"
+    ;;
+  kbench)
+    timeout 900 python scripts/kernel_bench.py "$@" > gpurun_out/kernel_bench.log 2>&1; echo "kbench rc=$?"; tail -n 60 gpurun_out/kernel_bench.log
+    ;;
+  *) echo "unknown: $what"; exit 2;;
+esac

@@ -207,7 +207,7 @@ def test_alexnet_bn_variant_both_arms_against_float64():
     weight gradient. Each arm is compared here with a float64 model. The difference is not a BN error: the convolution
     producers round their inputs to TF32, so two activations one fp32 ulp apart (different but equally valid BN
     arithmetic) can land on different TF32 values 5e-4 apart; five conv+BN layers amplify that to ~1e-2 between ANY two
-    fp32 implementations (scripts/debug_bn.py: layer outputs drift 5e-7 -> 2e-3). Both arms must sit within the TF32
+    fp32 implementations (measured in round 1, layer by layer: outputs drift 5e-7 -> 2e-3). Both arms must sit within the TF32
     bound of the float64 truth, and neither may be worse than 3x the other."""
     torch.manual_seed(1)
     m = AlexNet(bn=True, dropout=0.0, mode="tf32")
