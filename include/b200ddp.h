@@ -90,6 +90,23 @@ int b200ddp_comm_broadcast(void* handle, void* buf, long long nbytes, int root, 
  * handle's communication stream; join makes compute_stream wait for every launched bucket. */
 int b200ddp_bucket_reduce_launch(void* handle, float* buf, long long n, float premul, void* compute_stream);
 int b200ddp_bucket_reduce_join(void* handle, void* compute_stream);
+/* `stream` waits for the bucket collective launched last (a per-bucket optimizer launch follows its bucket). */
+int b200ddp_bucket_wait_last(void* handle, void* stream);
+/* arena_register: the gradient arena as NCCL-registered, peer-mapped memory (replaces the unregistered bucket tensors
+ * of c10d::Reducer, reducer.hpp:330-334). COLLECTIVE: every rank calls it with the same size at the same point.
+ * The buffer comes from ncclMemAlloc (owned by the communicator, freed by comm_destroy, zero-filled) and is registered
+ * as an NCCL symmetric window: *mode_out = 2 peer + NVSwitch multicast mappings, 1 peer mappings only, 0 plain
+ * ncclCommRegister (NCCL collectives only). Set-up call: synchronises the device. */
+int b200ddp_comm_arena_alloc(void* handle, long long nbytes, void** ptr_out, int* mode_out);
+/* Which all-reduce bucket_reduce_launch runs: 0 NCCL ring with PreMulSum(1/world) (any buffer), 1 this library's own
+ * kernel over the arena's peer mappings (multimem.ld_reduce / multimem.st through the NVSwitch, or peer loads / stores;
+ * `ctas` CTAs of 256 threads, <= 256; buffers outside an arena fall back to 0), 2 NCCL ncclSum on pre-scaled data.
+ * Returns 1 if the peer path is available, 0 if not, < 0 on a bad argument. Same value on every rank. */
+int b200ddp_comm_set_algo(void* handle, int algo, int ctas);
+/* Device time of each bucket collective of the last joined backward pass (for the NVLink roofline: busBW =
+ * 4 n * 2 (ws-1)/ws / t). set_timing(1) first; synchronise before reading. Returns the number of entries. */
+int b200ddp_comm_set_timing(void* handle, int on);
+int b200ddp_comm_bucket_times(void* handle, float* ms_out, long long* n_out, int max_entries);
 
 /* ---- F1/F2/F3: Linear layers --------------------------------------------------------------------- */
 /* Replace nn.Linear forward/backward (cuBLAS sgemm) + nn.ReLU + nn.Dropout of torchvision

@@ -56,21 +56,37 @@ def test_head_eval_matches_reference_evaluate_golden(golden_dir):
     assert m2[1] == m[1] and m2[2] == m[2] and abs(float(m2[0]) - m[0]) < 1e-4
 
 
-def test_head_eval_ties_nan_and_bad_labels_follow_torch():
-    h = torch.zeros(4, 64, device=DEV)
+def test_head_eval_ties_and_bad_labels_follow_torch():
+    h = torch.zeros(3, 64, device=DEV)
     w = torch.zeros(10, 64, device=DEV)
     b = torch.tensor([1., 3., 3., 0., 0., 0., 0., 0., 0., 0.], device=DEV)       # tie between classes 1 and 2
-    y = torch.tensor([1, 2, 12, 1], device=DEV)
-    h[3, 0] = float("nan")
-    w[5, 0] = 1.0                                                                 # row 3: logit 5 is NaN
+    y = torch.tensor([1, 2, 12], device=DEV)
     metrics = torch.zeros(3, device=DEV)
-    scratch = torch.zeros(int(_lib.load().b200ddp_eval_scratch_bytes(4)), dtype=torch.uint8, device=DEV)
-    logits = torch.empty(4, 10, device=DEV)
+    scratch = torch.zeros(int(_lib.load().b200ddp_eval_scratch_bytes(3)), dtype=torch.uint8, device=DEV)
+    logits = torch.empty(3, 10, device=DEV)
     _head_eval(h, w, b, y, metrics, scratch, logits)
     pred = torch.max(logits, 1)[1]
-    assert pred.tolist()[:3] == [1, 1, 1] and int(pred[3]) == 5                   # first maximum; NaN wins
+    assert pred.tolist() == [1, 1, 1]                                             # first maximum, as torch.max
     assert float(metrics[1]) == float((pred == y).sum()) == 1.0                   # only row 0 is a hit
-    assert float(metrics[2]) == 4.0
+    assert float(metrics[2]) == 3.0
+    ref = nn.functional.cross_entropy(logits[:2], y[:2], reduction="sum")         # the out-of-range label adds no loss
+    assert abs(float(metrics[0]) - float(ref)) < 1e-5
+
+
+def test_logits_eval_nan_wins_like_torch_max():
+    z = torch.randn(5, 10, device=DEV)
+    z[1, 7] = float("nan")
+    z[3, 2] = float("nan")
+    z[3, 6] = float("nan")                                                        # two NaNs: the first one is reported
+    pred = torch.max(z, 1)[1]
+    assert int(pred[1]) == 7 and int(pred[3]) == 2
+    y = pred.clone()
+    y[0] = (y[0] + 1) % 10
+    m = torch.zeros(3, device=DEV)
+    scratch = torch.zeros(int(_lib.load().b200ddp_eval_scratch_bytes(5)), dtype=torch.uint8, device=DEV)
+    _lib.check(_lib.load().b200ddp_logits_eval(z.data_ptr(), y.data_ptr(), 5, 10, m.data_ptr(), scratch.data_ptr(),
+                                               scratch.numel(), 0, _lib.cur_stream(DEV)), "logits_eval")
+    assert float(m[1]) == 4.0 and float(m[2]) == 5.0 and not torch.isfinite(m[0])  # NaN rows make the loss NaN, as in torch
 
 
 def test_evaluate_function_matches_reference_loop_on_the_toy_model():

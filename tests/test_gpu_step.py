@@ -74,38 +74,60 @@ def test_loss_and_gradients_match_torch(mode, tol_loss, tol_grad):
 
 
 def test_five_adam_steps_track_torch_in_strict_mode():
+    """Strict mode end to end (fp32 SIMT convolutions, Linear, loss, fused Adam) over five optimizer steps. Adam turns
+    rounding-level gradient differences into +-lr parameter moves, so two correct fp32 implementations drift apart
+    step by step; the yardstick is therefore a float64 run of the same stock model: ours must stay as close to it as
+    the tolerance or 3x stock fp32 torch's own distance, whichever is larger."""
+    import copy
     old = torch.backends.cudnn.allow_tf32
     torch.backends.cudnn.allow_tf32 = False
     try:
         tv, ours = _pair("fp32")
+        tv64 = copy.deepcopy(tv).double()
         ddp = b200ddp.DistributedDataParallel(ours, device_ids=[0])
         opt = b200ddp.optim.Adam(ddp.parameters(), lr=1e-4)
         opt_ref = torch.optim.Adam(tv.parameters(), lr=1e-4)
+        opt64 = torch.optim.Adam(tv64.parameters(), lr=1e-4)
         crit, crit_ref = b200ddp.CrossEntropyLoss(), nn.CrossEntropyLoss()
         x, y = rl.synthetic_pool(5 * 16, seed=7)
         for s in range(5):
             xb, yb = x[s * 16:(s + 1) * 16].to(DEV), y[s * 16:(s + 1) * 16].to(DEV)
             opt.zero_grad()
             opt_ref.zero_grad()
+            opt64.zero_grad()
             la = crit(ddp(xb), yb)
             la.backward()
             lb = crit_ref(tv(xb), yb)
             lb.backward()
-            before = _lib.launch_count()
+            l64 = crit_ref(tv64(xb.double()), yb)
+            l64.backward()
             opt.step()
-            assert _lib.launch_count() == before + 1          # ONE fused launch over the arena
             opt_ref.step()
-            assert abs(float(la) - float(lb)) < 2e-4 * abs(float(lb)), s
+            opt64.step()
+            e_ours, e_torch = abs(float(la) - float(l64)), abs(float(lb) - float(l64))
+            assert e_ours < max(2e-5 * abs(float(l64)), 3 * e_torch), (s, e_ours, e_torch)
         # gradients of the big Linear layers were written straight into the arena (no pack copy)
         for name in ("classifier.1.weight", "classifier.4.weight", "classifier.6.bias"):
             p = dict(ours.named_parameters())[name]
             assert ddp.arena.grad_in_arena(ddp.arena.index_of(p))
-        for (k, p), (_, q) in zip(ours.named_parameters(), tv.named_parameters()):
-            assert _rel_l2(p.detach(), q.detach()) < 5e-3, k     # 5 Adam steps amplify fp32 rounding (m/sqrt(v))
+        for (k, p), (_, q), (_, r) in zip(ours.named_parameters(), tv.named_parameters(), tv64.named_parameters()):
+            e_ours, e_torch = _rel_l2(p.detach(), r.detach()), _rel_l2(q.detach(), r.detach())
+            assert e_ours < max(1e-4, 3 * e_torch), (k, e_ours, e_torch)
         sd = ddp.state_dict()
         assert list(sd)[0] == "module.features.0.weight" and len(sd) == 16
     finally:
         torch.backends.cudnn.allow_tf32 = old
+
+
+def test_adam_step_is_one_launch_over_the_arena():
+    torch.manual_seed(0)
+    from b200ddp import nn as bnn
+    net = nn.Sequential(bnn.Linear(64, 64, relu=True, mode="fp32"), bnn.Linear(64, 10, mode="fp32")).to(DEV)
+    opt = b200ddp.optim.Adam(b200ddp.optim.flatten_parameters(net).params, lr=1e-3)
+    b200ddp.CrossEntropyLoss()(net(torch.randn(8, 64, device=DEV)), torch.zeros(8, dtype=torch.int64, device=DEV)).backward()
+    before = _lib.launch_count()
+    opt.step()
+    assert _lib.launch_count() == before + 1
 
 
 @pytest.mark.parametrize("mode,tol", [("fp32", 3e-3), ("tf32", 2e-2)])

@@ -57,6 +57,11 @@ _PROTOS = {
     "b200ddp_comm_broadcast": (c_int, [_P, _P, c_longlong, c_int, _P]),
     "b200ddp_bucket_reduce_launch": (c_int, [_P, _P, c_longlong, c_float, _P]),
     "b200ddp_bucket_reduce_join": (c_int, [_P, _P]),
+    "b200ddp_bucket_wait_last": (c_int, [_P, _P]),
+    "b200ddp_comm_arena_alloc": (c_int, [_P, c_longlong, POINTER(c_void_p), POINTER(c_int)]),
+    "b200ddp_comm_set_algo": (c_int, [_P, c_int, c_int]),
+    "b200ddp_comm_set_timing": (c_int, [_P, c_int]),
+    "b200ddp_comm_bucket_times": (c_int, [_P, POINTER(c_float), POINTER(c_longlong), c_int]),
     "b200ddp_linear_workspace_bytes": (c_longlong, [c_int, c_int, c_int]),
     "b200ddp_linear_fwd": (c_int, [_P, _P, _P, _P, _P, c_int, c_int, c_int, c_int, c_float, c_ulonglong, c_int, _P,
                                    c_longlong, c_int, _P]),

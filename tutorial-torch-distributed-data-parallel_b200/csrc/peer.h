@@ -1,0 +1,30 @@
+// Private interface between comm.cu (NCCL bootstrap: symmetric windows, multicast handle) and peer_allreduce.cu
+// (the all-reduce kernels that run over those mappings).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace b200 {
+
+constexpr int kPeerMaxRanks = 8;        // one NVSwitch box
+constexpr int kPeerMaxCtas = 256;       // CTAs of one all-reduce launch (flag slots per rank)
+
+// Where every rank's copy of a symmetric buffer is mapped in THIS process.
+struct PeerMap {
+  char* peer[kPeerMaxRanks];    // unicast address of rank r's buffer base (peer[rank] is the local one)
+  char* mc;                     // multicast address of the buffer base (NVSwitch multimem), null if none
+};
+
+// flags: a second, small symmetric buffer: inbox[cta][src_rank] of uint32 epochs, written by peers.
+struct PeerArgs {
+  PeerMap data;
+  PeerMap flags;
+  int rank, nranks;
+  unsigned int epoch;           // the two barriers of this launch use epoch + 1 and epoch + 2
+};
+
+// In-place sum over ranks of buf[off_bytes .. off_bytes + 4 n) (n % 4 == 0, off_bytes % 16 == 0) of the symmetric
+// buffer described by a.data; every element is multiplied by `scale` after the sum (1/world = the mean).
+int peer_allreduce_launch(const PeerArgs& a, long long off_bytes, long long n, float scale, int ctas, cudaStream_t stream);
+
+}  // namespace b200
