@@ -330,3 +330,70 @@ def case_syncbn_two_ranks(rank, world, out_dir, dev):
     assert torch.allclose(net[1].running_var, ref[1].running_var, rtol=1e-4, atol=1e-6)
     for (k, p), (_, q) in zip(net.named_parameters(), ref.named_parameters()):
         assert torch.allclose(p.grad, q.grad, rtol=2e-3, atol=1e-5), k
+
+
+def case_own_allreduce_known_values(rank, world, out_dir, dev):
+    """R4: the library's own all-reduce kernel over the registered arena (multimem / peer loads), through the C ABI,
+    against exact expectations and against torch.distributed's NCCL all-reduce: whole arena, ranges at offsets, sizes
+    that do not divide by the world size, many launches in a row (flag epochs), several CTA counts."""
+    from b200ddp.comm import get_comm
+    comm = get_comm(dev, None)
+    n = 3 * 1024 * 1024 + 64 * 5
+    buf = comm.arena_alloc(n)
+    assert buf.is_cuda and buf.numel() == n and float(buf.abs().sum()) == 0.0
+    peer = comm.set_algo("own")
+    if comm.arena_mode < 1 or not peer:
+        import pytest
+        print("peer path unavailable on this box (arena_mode %d)" % comm.arena_mode)
+        comm.set_algo("ring")
+    idx = torch.arange(n, device=dev, dtype=torch.float32)
+    for it, (start, cnt, ctas) in enumerate([(0, n, 64), (64, 4096, 8), (1 << 20, (1 << 20) + 64 * 3, 200), (0, n, 1),
+                                             (n - 64, 64, 16)] * 3):
+        comm.set_algo("own" if peer else "ring", ctas)
+        buf.copy_((idx % 1000) + 7.0 * (rank + 1) + it)                 # small integers: sums are exact in fp32
+        want = buf.clone()
+        seg = want[start:start + cnt].clone()
+        dist.all_reduce(seg)
+        want[start:start + cnt] = seg / world
+        torch.cuda.synchronize()
+        comm.bucket_reduce_launch(buf[start:start + cnt].data_ptr(), cnt, 1.0 / world, dev)
+        comm.bucket_reduce_join(dev)
+        torch.cuda.synchronize()
+        assert torch.equal(buf, want), (it, start, cnt, float((buf - want).abs().max()))
+    # random data: equal to NCCL's sum up to fp32 summation order, and bit-identical on all ranks
+    g = torch.Generator(device=dev).manual_seed(100 + rank)
+    buf.copy_(torch.randn(n, device=dev, generator=g))
+    ref = buf.clone()
+    dist.all_reduce(ref)
+    ref /= world
+    comm.bucket_reduce_launch(buf.data_ptr(), n, 1.0 / world, dev)
+    comm.bucket_reduce_join(dev)
+    torch.cuda.synchronize()
+    assert torch.allclose(buf, ref, rtol=1e-6, atol=1e-6)
+    mine = [torch.empty_like(buf) for _ in range(world)]
+    dist.all_gather(mine, buf)
+    assert all(torch.equal(mine[0], t) for t in mine)
+    with open(os.path.join(out_dir, f"arena_mode_rank{rank}.txt"), "w") as fh:
+        fh.write(f"{comm.arena_mode} {int(peer)}")
+
+
+def case_fused_adam_in_backward_is_bitwise(rank, world, out_dir, dev):
+    """f4: per-bucket Adam launched as each bucket's all-reduce completes == the one-launch step after backward."""
+    import b200ddp
+    outs = []
+    for overlap in (True, False):
+        model = _mlp(seed=3).to(dev)
+        ddp = b200ddp.DistributedDataParallel(model)
+        opt = b200ddp.optim.Adam(ddp.parameters(), lr=1e-2, overlap_backward=overlap)
+        for s in range(4):
+            x, y = _data(rank, s)
+            opt.zero_grad()
+            nn.functional.cross_entropy(ddp(x.to(dev)), y.to(dev)).backward()
+            if overlap and dev.type == "cuda":
+                assert ddp.reducer.fused_applied
+            opt.step()
+        assert float(opt.state[next(iter(model.parameters()))]["step"]) == 4.0
+        outs.append(torch.cat([p.detach().reshape(-1) for p in model.parameters()]).clone())
+    assert torch.equal(outs[0], outs[1])
+    ps = _gather_params(model, world)
+    assert all(torch.equal(ps[0], t) for t in ps)

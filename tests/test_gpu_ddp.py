@@ -28,3 +28,8 @@ def test_alexnet_ddp_matches_stock_ddp(tmp_path):
 
 def test_syncbn_two_ranks_matches_global_batch(tmp_path):
     _spawn(_workers.run, "syncbn_two_ranks", tmp_path)
+
+
+def test_own_allreduce_kernel_known_values(tmp_path):
+    _spawn(_workers.run, "own_allreduce_known_values", tmp_path)
+    print("arena mode / peer path:", open(os.path.join(str(tmp_path), "arena_mode_rank0.txt")).read())

@@ -354,3 +354,27 @@ def test_cross_entropy_ignore_index_and_bad_label():
     # the report is one-shot: the next clean call works
     loss = b200ddp.CrossEntropyLoss()(z.detach().requires_grad_(), torch.zeros(6, dtype=torch.int64, device=DEV))
     assert torch.isfinite(loss)
+
+
+def test_fused_adam_in_backward_single_gpu_is_bitwise():
+    """f4 on one GPU: Adam launched per bucket on the optimizer stream during backward (while the convolution backward
+    still runs) gives the same parameters, bit for bit, as the one-launch step after backward."""
+    x, y = rl.synthetic_pool(3 * 16, seed=8)
+    outs = []
+    for overlap in (True, False):
+        torch.manual_seed(4)
+        model = AlexNet(dropout=0.0, mode="tf32").to(DEV)
+        ddp = b200ddp.DistributedDataParallel(model, device_ids=[0])
+        opt = b200ddp.optim.Adam(ddp.parameters(), lr=1e-3, overlap_backward=overlap)
+        crit = b200ddp.CrossEntropyLoss()
+        for s in range(3):
+            opt.zero_grad()
+            crit(ddp(x[s * 16:(s + 1) * 16].to(DEV)), y[s * 16:(s + 1) * 16].to(DEV)).backward()
+            assert ddp.reducer.fused_applied == overlap
+            before = _lib.launch_count()
+            opt.step()
+            assert _lib.launch_count() == before + (0 if overlap else 1)
+        torch.cuda.synchronize()
+        outs.append(ddp.arena.p_flat.clone())
+        assert float(opt.state[model.classifier[6].weight]["step"]) == 3.0
+    assert torch.equal(outs[0], outs[1])

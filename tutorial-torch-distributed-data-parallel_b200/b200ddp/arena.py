@@ -20,7 +20,9 @@ ALIGN_ELEMS = 64
 
 
 class FlatArena:
-    def __init__(self, params: Iterable[torch.nn.Parameter]) -> None:
+    def __init__(self, params: Iterable[torch.nn.Parameter], grad_alloc=None) -> None:
+        """`grad_alloc(numel) -> fp32 zeros tensor` (optional) supplies the gradient arena's memory, e.g. NCCL-registered
+        peer-mapped memory from NativeComm.arena_alloc; default: a plain torch allocation."""
         self.params: List[torch.nn.Parameter] = list(params)
         if not self.params:
             raise ValueError("FlatArena needs at least one parameter")
@@ -38,7 +40,9 @@ class FlatArena:
             off += (p.numel() + ALIGN_ELEMS - 1) // ALIGN_ELEMS * ALIGN_ELEMS
         self.numel = off
         self.p_flat = torch.zeros(off, dtype=torch.float32, device=dev)
-        self.g_flat = torch.zeros(off, dtype=torch.float32, device=dev)
+        self.g_flat = grad_alloc(off) if grad_alloc is not None else torch.zeros(off, dtype=torch.float32, device=dev)
+        if self.g_flat.numel() != off or self.g_flat.dtype != torch.float32 or self.g_flat.device != dev:
+            raise ValueError("grad_alloc returned a buffer of the wrong size / dtype / device")
         # optimizer moments are created lazily by b200ddp.optim.Adam with the same layout
         self.m_flat: Optional[torch.Tensor] = None
         self.v_flat: Optional[torch.Tensor] = None

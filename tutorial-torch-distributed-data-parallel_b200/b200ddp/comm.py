@@ -26,6 +26,9 @@ class NativeComm:
         self.rank = rank
         self.world = world
         self.device = device
+        self.arena_mode = 0
+        self.algo = "ring"
+        self._arenas = []
 
     # thin wrappers; all stream ordered
     def allreduce_(self, t: torch.Tensor, premul: float = 1.0, stream: Optional[int] = None) -> None:
@@ -48,6 +51,50 @@ class NativeComm:
         L = _lib.load()
         _lib.check(L.b200ddp_bucket_reduce_launch(self.handle, ptr, n, premul, _lib.cur_stream(device)),
                    "bucket_reduce_launch")
+
+    def bucket_wait_last(self, stream: int) -> None:
+        """`stream` (a raw cudaStream_t) waits for the bucket collective launched last."""
+        _lib.check(_lib.load().b200ddp_bucket_wait_last(self.handle, stream), "bucket_wait_last")
+
+    # ---- registered / peer-mapped gradient arena (R4) -----------------------------------------------------
+    def arena_alloc(self, numel: int) -> torch.Tensor:
+        """COLLECTIVE. fp32 tensor of `numel` zeros in memory from ncclMemAlloc, registered with the communicator as
+        a symmetric window (b200ddp_comm_arena_alloc). `self.arena_mode`: 2 = peers + NVSwitch multicast mapped,
+        1 = peers mapped, 0 = registered for NCCL's own collectives only. The communicator owns the memory."""
+        ptr, mode = ctypes.c_void_p(), ctypes.c_int(0)
+        _lib.check(_lib.load().b200ddp_comm_arena_alloc(self.handle, int(numel) * 4, ctypes.byref(ptr), ctypes.byref(mode)),
+                   "comm_arena_alloc")
+        self.arena_mode = int(mode.value)
+
+        class _Foreign:      # torch.as_tensor wraps (does not copy) an object with __cuda_array_interface__
+            pass
+        holder = _Foreign()
+        holder.__cuda_array_interface__ = {"shape": (int(numel),), "typestr": "<f4", "data": (int(ptr.value), False),
+                                           "version": 2, "strides": None}
+        t = torch.as_tensor(holder, device=self.device)
+        assert t.data_ptr() == ptr.value and t.dtype == torch.float32
+        self._arenas.append((holder, t))
+        return t
+
+    def set_algo(self, algo: str, ctas: int = 0) -> bool:
+        """'ring' (NCCL PreMulSum), 'own' (this library's peer-memory kernel) or 'sum' (NCCL ncclSum, pre-scaled data).
+        Returns whether the peer path exists on this system."""
+        code = {"ring": 0, "premul": 0, "own": 1, "peer": 1, "sum": 2}[algo]
+        rc = int(_lib.load().b200ddp_comm_set_algo(self.handle, code, int(ctas)))
+        if rc < 0:
+            raise _lib.B200Error("comm_set_algo: bad argument")
+        self.algo = algo
+        return rc > 0
+
+    def set_timing(self, on: bool) -> None:
+        _lib.check(_lib.load().b200ddp_comm_set_timing(self.handle, int(bool(on))), "comm_set_timing")
+
+    def bucket_times(self):
+        """[(ms, elements)] of the bucket collectives of the last joined backward (synchronise first)."""
+        ms = (ctypes.c_float * 64)()
+        n = (ctypes.c_longlong * 64)()
+        k = int(_lib.load().b200ddp_comm_bucket_times(self.handle, ms, n, 64))
+        return [(float(ms[i]), int(n[i])) for i in range(max(k, 0))]
 
     def bucket_reduce_join(self, device) -> None:
         L = _lib.load()
@@ -89,13 +136,25 @@ def get_comm(device: torch.device, process_group=None) -> Optional[NativeComm]:
     _lib.check(L.b200ddp_comm_create(ctypes.byref(handle), uid, rank, world, dev_index), "comm_create")
     comm = NativeComm(handle.value, rank, world, device)
     _COMMS[key] = comm
-    # leave the SMs of the collective's channels out of the one-wave grid plans (see b200ddp/__init__.py)
+    reserve_sms_for_nccl(True)
+    return comm
+
+
+def reserve_sms_for_nccl(on: bool) -> None:
+    """NCCL's persistent kernels own one SM per channel while a collective runs beside the backward pass: leave those
+    SMs out of the one-wave grid plans (see b200ddp/__init__.py). Our own all-reduce kernel is built to co-reside with
+    the convolution CTAs instead (peer_allreduce.cu), so with it the compute kernels plan for the whole device."""
+    L = _lib.load()
+    if not on:
+        L.b200ddp_set_sm_budget(0)
+        return
     try:
         channels = int(os.environ.get("NCCL_MAX_NCHANNELS", "16"))
     except ValueError:
         channels = 16
-    L.b200ddp_set_sm_budget(148 - max(0, min(channels, 32)))
-    return comm
+    n = ctypes.c_int(148)
+    L.b200ddp_device_info(torch.cuda.current_device(), ctypes.byref(n), None, None)
+    L.b200ddp_set_sm_budget(max(16, n.value - max(0, min(channels, 32))))
 
 
 def destroy_all() -> None:

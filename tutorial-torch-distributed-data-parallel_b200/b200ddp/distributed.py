@@ -17,6 +17,7 @@ local gradient is not finite.
 """
 from __future__ import annotations
 
+import os
 import warnings
 from contextlib import contextmanager
 from typing import Optional
@@ -81,8 +82,13 @@ class DistributedDataParallel(nn.Module):
         else:
             _warn_plumbing()
             self.comm = None
-        # reverse registration order ~ the order in which gradients become ready
-        self.arena = FlatArena(list(reversed(params)))
+        # reverse registration order ~ the order in which gradients become ready.
+        # With more than one rank the gradient arena lives in NCCL-registered, peer-mapped memory (arena_register,
+        # SURVEY 8(b)): the all-reduce then runs as this library's own kernel over the NVSwitch (peer_allreduce.cu).
+        grad_alloc = None
+        if self.on_gpu and self.comm is not None and os.environ.get("B200DDP_ARENA", "registered") != "plain":
+            grad_alloc = self.comm.arena_alloc
+        self.arena = FlatArena(list(reversed(params)), grad_alloc=grad_alloc)
         self._sync_module_states()
         self.reducer = Reducer(self.arena, process_group, bucket_cap_mb=bucket_cap_mb,
                                clip_grad_value=clip_grad_value, clip_grad_norm=clip_grad_norm,
@@ -122,6 +128,8 @@ class DistributedDataParallel(nn.Module):
     def forward(self, *inputs, **kwargs):
         if torch.is_grad_enabled() and self.require_backward_grad_sync:
             self.reducer.require_sync = True
+            # no gradient pending anywhere: the backward pass that follows may apply the optimizer bucket by bucket
+            self.reducer.fresh_grads = all(p.grad is None for p in self.arena.params)
             if self.broadcast_buffers and self.world_size > 1 and self.training and any(
                     True for _ in self.module.buffers()):
                 with torch.no_grad():
@@ -166,6 +174,12 @@ class DistributedDataParallel(nn.Module):
         finally:
             self.require_backward_grad_sync = old
             self.reducer.require_sync = old
+
+    def set_clipping(self, clip_grad_value: Optional[float] = None, clip_grad_norm: Optional[float] = None,
+                     nonfinite: str = "propagate") -> None:
+        """Change the clip-before-aggregation mode (README.md:92-95) of an existing wrapper; takes effect at the next
+        backward pass. Every rank must make the same call."""
+        self.reducer.configure_clipping(clip_grad_value, clip_grad_norm, nonfinite)
 
     # ---- introspection used by tests / logging ---------------------------------------------------------
     def bucket_sizes(self):

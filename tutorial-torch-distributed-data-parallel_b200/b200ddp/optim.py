@@ -14,6 +14,8 @@ Loose CUDA parameters get one launch each. CPU parameters run the same arithmeti
 from __future__ import annotations
 
 import math
+import os
+import weakref
 from typing import Optional
 
 import torch
@@ -34,7 +36,7 @@ def flatten_parameters(module_or_params) -> FlatArena:
 class Adam(Optimizer):
     def __init__(self, params, lr: float = 1e-3, betas=(0.9, 0.999), eps: float = 1e-8, weight_decay: float = 0.0,
                  amsgrad: bool = False, *, maximize: bool = False, foreach=None, capturable: bool = False,
-                 differentiable: bool = False, fused=None) -> None:
+                 differentiable: bool = False, fused=None, overlap_backward: Optional[bool] = None) -> None:
         if not 0.0 <= lr:
             raise ValueError(f"Invalid learning rate: {lr}")
         if not 0.0 <= eps:
@@ -51,6 +53,56 @@ class Adam(Optimizer):
         defaults = dict(lr=lr, betas=betas, eps=eps, weight_decay=weight_decay, amsgrad=False, maximize=False,
                         foreach=None, capturable=False, differentiable=False, fused=None)
         super().__init__(params, defaults)
+        # Step inside backward: when the parameters are the arena of a b200ddp DistributedDataParallel, the wrapper's
+        # reducer launches this optimizer's kernel per gradient bucket as each bucket's all-reduce completes, overlapped
+        # with the rest of backward; `step()` then only counts the step. `.grad` is untouched, parameters are final
+        # when backward() returns (so gradient surgery BETWEEN backward() and step() has no effect: switch it off with
+        # overlap_backward=False or B200DDP_ADAM_IN_BACKWARD=0 if you do that). Identical parameters either way.
+        self.overlap_backward = (os.environ.get("B200DDP_ADAM_IN_BACKWARD", "1") != "0" if overlap_backward is None
+                                 else bool(overlap_backward))
+        self._registered_with = None
+        self._register_with_reducer()
+
+    # ---- step inside backward ---------------------------------------------------------------------------------
+    def _register_with_reducer(self) -> None:
+        """Offer this optimizer to the reducer that owns the parameters' arena (if any). Called at construction and
+        again from step(): reference multi-GPU-training-accelerate.py:126-129 builds the optimizer BEFORE prepare()
+        wraps the model, i.e. before the arena exists."""
+        if not self.overlap_backward or self._registered_with is not None or len(self.param_groups) != 1:
+            return
+        arena = arena_of(self.param_groups[0]["params"])
+        ref = getattr(arena, "reducer", None) if arena is not None else None
+        red = ref() if ref is not None else None
+        if red is not None and arena.device.type == "cuda":
+            red.fused_opt = weakref.ref(self)
+            self._registered_with = ref
+
+    def _can_fuse(self, arena: FlatArena) -> bool:
+        if not self.overlap_backward or len(self.param_groups) != 1:
+            return False
+        return arena_of(self.param_groups[0]["params"]) is arena
+
+    def _shared_step(self, arena: FlatArena):
+        arena.ensure_moments()
+        first = self._init_state(arena.params[0])
+        for p in arena.params[1:]:      # one shared step tensor for all parameters of the arena (they advance together)
+            st = self._init_state(p)
+            st["step"] = first["step"]
+        return first
+
+    def _next_step_count(self, arena: FlatArena) -> int:
+        return int(self._shared_step(arena)["step"].item()) + 1
+
+    def _launch_range(self, arena: FlatArena, start: int, end: int, t: int, stream: int) -> None:
+        """Adam on arena elements [start, end) with step count t, on `stream` (called by the reducer per bucket)."""
+        g = self.param_groups[0]
+        (b1, b2) = g["betas"]
+        off = 4 * start
+        _lib.check(_lib.load().b200ddp_adam_step_flat(arena.p_flat.data_ptr() + off, arena.g_flat.data_ptr() + off,
+                                                      arena.m_flat.data_ptr() + off, arena.v_flat.data_ptr() + off,
+                                                      end - start, float(g["lr"]), float(b1), float(b2), float(g["eps"]),
+                                                      float(g["weight_decay"]), int(t), None, _lib.dev_index(arena.p_flat),
+                                                      stream), "adam_step_flat(bucket)")
 
     # ---- state ------------------------------------------------------------------------------------------
     def _init_state(self, p) -> dict:
@@ -87,6 +139,13 @@ class Adam(Optimizer):
                 loss = closure()
         from .nn import join_side_work
         join_side_work()
+        self._register_with_reducer()
+        red = self._registered_with() if self._registered_with is not None else None
+        if red is not None and red.fused_applied:
+            # the reducer already ran this step's update bucket by bucket during backward (and joined the streams)
+            red.fused_applied = False
+            self._shared_step(red.arena)["step"] += 1
+            return loss
         for group in self.param_groups:
             params = [p for p in group["params"] if p.grad is not None]
             if not params:
@@ -109,12 +168,7 @@ class Adam(Optimizer):
         return loss
 
     def _step_flat(self, arena: FlatArena, group, lr, b1, b2, eps, wd) -> None:
-        arena.ensure_moments()
-        first = self._init_state(arena.params[0])
-        # one shared step tensor for all parameters of the arena (they always advance together)
-        for p in arena.params[1:]:
-            st = self._init_state(p)
-            st["step"] = first["step"]
+        first = self._shared_step(arena)
         first["step"] += 1
         t = int(first["step"].item())
         L = _lib.load()

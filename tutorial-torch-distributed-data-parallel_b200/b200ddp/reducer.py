@@ -22,6 +22,7 @@ With CPU tensors (gloo) the same host logic runs with torch ops in place of the 
 from __future__ import annotations
 
 import ctypes
+import weakref
 from typing import List, Optional
 
 import os
@@ -81,15 +82,39 @@ class Reducer:
         self.comm = comm
         self.clip_value = None if clip_grad_value is None else float(clip_grad_value)
         self.clip_norm = None if clip_grad_norm is None else float(clip_grad_norm)
-        # B200DDP_ALLREDUCE=sum: plain-sum all-reduce of pre-scaled gradients (see DistributedDataParallel.forward),
-        # which NCCL runs as NVLS on NVSwitch. Measured on 8 x B200 with unregistered buffers it is SLOWER than the
-        # default RING + PreMulSum path (3.04 vs 2.80 ms/step), so it stays opt-in. The clip-before-aggregation
-        # modes always use PreMulSum so that their thresholds act on unscaled local gradients.
-        self.prescale = (arena.device.type == "cuda" and self.clip_value is None and self.clip_norm is None
-                         and os.environ.get("B200DDP_ALLREDUCE", "premul") == "sum")
+        # Which all-reduce runs (B200DDP_ALLREDUCE):
+        #   own  (default) this library's kernel over the registered arena's NVSwitch multicast / peer mappings
+        #        (peer_allreduce.cu), 1/world folded in; needs comm.arena_mode >= 1, else falls back to ring;
+        #   ring NCCL all-reduce with a PreMulSum(1/world) operator (NCCL runs user-defined operators as RING);
+        #   sum  NCCL ncclSum on gradients pre-scaled by 1/world at the loss (see DistributedDataParallel.forward), which
+        #        NCCL may run as NVLS; the clip-before-aggregation modes never pre-scale (thresholds act on raw gradients).
+        self.algo = "ring"
+        if self.on_gpu and self.world > 1 and comm is not None:
+            from . import comm as _comm_mod
+            want = os.environ.get("B200DDP_ALLREDUCE", "own")
+            in_arena = getattr(comm, "arena_mode", 0) >= 1 and any(t.data_ptr() == arena.g_flat.data_ptr()
+                                                                    for _, t in getattr(comm, "_arenas", []))
+            if want in ("own", "peer") and in_arena and comm.set_algo("own", int(os.environ.get("B200DDP_AR_CTAS", "0"))):
+                self.algo = "own"
+            elif want == "sum":
+                comm.set_algo("sum")
+                self.algo = "sum"
+            else:
+                comm.set_algo("ring")
+            _comm_mod.reserve_sms_for_nccl(self.algo != "own")
         self.pass_prescaled = False
         self.nonfinite_zero = nonfinite == "zero"
+        self.prescale = False
+        self._update_prescale()
         self.require_sync = True
+        # optimizer step per bucket during backward (set by b200ddp.optim.Adam, see _fused_adam)
+        self.fused_opt = None
+        self.fresh_grads = False
+        self._fused_now = None
+        self._fused_t = 0
+        self.fused_applied = False
+        self.opt_stream = torch.cuda.Stream(arena.device) if self.on_gpu else None
+        arena.reducer = weakref.ref(self)
         self.last_local_norm: Optional[torch.Tensor] = None
 
         params = arena.params
@@ -120,14 +145,7 @@ class Reducer:
         self._tail_prefix = None           # (bucket index, set of prefix members, prefix end offset)
         self._tail_prefix_pending = 0
         self._tail_early = False
-        if (self.on_gpu and self.world > 1 and self.clip_value is None and self.clip_norm is None and self.buckets
-                and os.environ.get("B200DDP_TAIL_SPLIT", "1") != "0"):
-            last = self.buckets[-1]
-            if len(last.members) > 2:
-                prefix = last.members[:-2]
-                p_start, p_end = arena.span(prefix[0], prefix[-1])
-                if (p_end - p_start) * 4 >= (1 << 20):
-                    self._tail_prefix = (last.index, frozenset(prefix), p_end)
+        self._update_tail_prefix()
         if self.on_gpu:
             dev = arena.device
             self._sq = torch.zeros(1, dtype=torch.float32, device=dev)
@@ -136,6 +154,50 @@ class Reducer:
             nbytes = int(_lib.load().b200ddp_sqnorm_scratch_bytes())
             self._sq_scratch = torch.zeros(nbytes, dtype=torch.uint8, device=dev)
         self._hooks = [p.register_post_accumulate_grad_hook(self._make_hook(i)) for i, p in enumerate(params)]
+
+    def _update_prescale(self) -> None:
+        self.prescale = (self.on_gpu and self.clip_value is None and self.clip_norm is None and self.algo == "sum")
+
+    def _update_tail_prefix(self) -> None:
+        self._tail_prefix = None
+        arena = self.arena
+        if (self.on_gpu and self.world > 1 and self.clip_value is None and self.clip_norm is None and self.buckets
+                and os.environ.get("B200DDP_TAIL_SPLIT", "1") != "0"):
+            last = self.buckets[-1]
+            if len(last.members) > 2:
+                prefix = last.members[:-2]
+                p_start, p_end = arena.span(prefix[0], prefix[-1])
+                if (p_end - p_start) * 4 >= (1 << 20):
+                    self._tail_prefix = (last.index, frozenset(prefix), p_end)
+
+    def configure_clipping(self, clip_grad_value=None, clip_grad_norm=None, nonfinite: str = "propagate") -> None:
+        if clip_grad_value is not None and clip_grad_norm is not None:
+            raise ValueError("choose clip_grad_value or clip_grad_norm, not both")
+        if nonfinite not in ("propagate", "zero"):
+            raise ValueError("nonfinite must be 'propagate' or 'zero'")
+        self.clip_value = None if clip_grad_value is None else float(clip_grad_value)
+        self.clip_norm = None if clip_grad_norm is None else float(clip_grad_norm)
+        self.nonfinite_zero = nonfinite == "zero"
+        self._update_prescale()
+        self._update_tail_prefix()
+
+    # ---- optimizer step inside backward (the idea behind upstream's _register_fused_optim,
+    #      torch/nn/parallel/distributed.py:2097) ------------------------------------------------------------------
+    def _fused_adam(self, start: int, end: int) -> None:
+        """Adam on arena range [start, end) as soon as that range's averaged gradient exists: on a second stream, after
+        the range's all-reduce (or, single rank, after its producers), while backward goes on computing the earlier
+        layers' gradients. Same kernel and arithmetic as the one-launch step: parameters come out bit-identical."""
+        opt = self._fused_now
+        if opt is None or end <= start:
+            return
+        st = self.opt_stream
+        if self.world > 1:
+            self.comm.bucket_wait_last(st.cuda_stream)
+        else:
+            ev = torch.cuda.Event()
+            ev.record(torch.cuda.current_stream(self.arena.device))
+            st.wait_event(ev)
+        opt._launch_range(self.arena, start, end, self._fused_t, st.cuda_stream)
 
     # ---- public ------------------------------------------------------------------------------------
     def bucket_sizes_bytes(self) -> List[int]:
@@ -166,6 +228,14 @@ class Reducer:
         self._ready_order = []
         self._tail_early = False
         self._tail_prefix_pending = len(self._tail_prefix[1]) if self._tail_prefix is not None else 0
+        # fused optimizer: only for a backward pass that starts from empty gradients (no accumulation pending)
+        opt = self.fused_opt() if self.fused_opt is not None else None
+        self._fused_now = None
+        self.fused_applied = False
+        if opt is not None and self.on_gpu and self.fresh_grads and opt._can_fuse(self.arena):
+            self._fused_now = opt
+            self._fused_t = opt._next_step_count(self.arena)
+        self.fresh_grads = False
 
     def _on_grad_ready(self, i: int, param) -> None:
         if not self.require_sync:
@@ -203,6 +273,7 @@ class Reducer:
                 self.comm.bucket_reduce_launch(self.arena.g_flat[b.start:self._tail_prefix[2]].data_ptr(),
                                                self._tail_prefix[2] - b.start,
                                                1.0 if self.pass_prescaled else 1.0 / self.world, self.arena.device)
+                self._fused_adam(b.start, self._tail_prefix[2])
         if b.pending == 0:
             b.ready = True
             while self.next_bucket < len(self.buckets) and self.buckets[self.next_bucket].ready:
@@ -240,13 +311,18 @@ class Reducer:
     def _launch_allreduce(self, b: _Bucket) -> None:
         b.launched = True
         if self.world == 1:
+            if self.on_gpu:
+                self._fused_adam(b.start, b.end)
             return
         t = self._bucket_tensor(b)
         if self.on_gpu:
             premul = 1.0 if self.pass_prescaled else 1.0 / self.world
+            start = b.start
             if self._tail_early and self._tail_prefix is not None and b.index == self._tail_prefix[0]:
-                t = self.arena.g_flat[self._tail_prefix[2]:b.end]      # the prefix is already being reduced
+                start = self._tail_prefix[2]                           # the prefix is already being reduced
+                t = self.arena.g_flat[start:b.end]
             self.comm.bucket_reduce_launch(t.data_ptr(), t.numel(), premul, t.device)
+            self._fused_adam(start, b.end)
         else:
             t.mul_(1.0 / self.world)
             b.work = dist.all_reduce(t, group=self.pg, async_op=True)
@@ -264,6 +340,14 @@ class Reducer:
                 self.first_ready_order = list(self._ready_order)
             if self.clip_norm is not None:
                 self._clip_by_norm_then_reduce()
+            if self.on_gpu and self._fused_now is not None:
+                # every range has had its Adam launch: the compute stream joins the optimizer stream here, so that
+                # parameters are final for whatever the caller enqueues next; optimizer.step() only counts the step
+                done = torch.cuda.Event()
+                done.record(self.opt_stream)
+                torch.cuda.current_stream(self.arena.device).wait_event(done)
+                self.fused_applied = True
+                self._fused_now = None
             if self.world > 1:
                 if self.on_gpu:
                     self.comm.bucket_reduce_join(self.arena.device)
