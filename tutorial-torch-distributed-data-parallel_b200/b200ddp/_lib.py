@@ -217,8 +217,9 @@ class _TimedLib:
             return fn
 
         def timed(*args):
-            # plain integer arguments (sizes, flags) identify the call; pointers / stream handles are > 2^40
-            ints = tuple(a for a in args if isinstance(a, int) and not isinstance(a, bool) and 0 <= a < (1 << 40))
+            # plain integer arguments (sizes, flags) identify the call; pointers / stream handles are far larger
+            # (NCCL-allocated arenas sit at virtual addresses of a few tens of GB, so the cut is at 2^31)
+            ints = tuple(a for a in args if isinstance(a, int) and not isinstance(a, bool) and 0 <= a < (1 << 31))
             e0 = torch.cuda.Event(enable_timing=True)
             e1 = torch.cuda.Event(enable_timing=True)
             e0.record()

@@ -114,6 +114,9 @@ class Reducer:
         self._fused_t = 0
         self.fused_applied = False
         self.opt_stream = torch.cuda.Stream(arena.device) if self.on_gpu else None
+        # measurement knob (bench.py): run the step with every collective launch skipped - same kernels, same streams,
+        # no communication - so that "exposed communication" = step time - dry step time. Results are then local.
+        self.dry_run_collectives = False
         arena.reducer = weakref.ref(self)
         self.last_local_norm: Optional[torch.Tensor] = None
 
@@ -191,7 +194,7 @@ class Reducer:
         if opt is None or end <= start:
             return
         st = self.opt_stream
-        if self.world > 1:
+        if self.world > 1 and not self.dry_run_collectives:
             self.comm.bucket_wait_last(st.cuda_stream)
         else:
             ev = torch.cuda.Event()
@@ -270,9 +273,10 @@ class Reducer:
                 from .nn import join_side_work
                 join_side_work(self.arena.device)
                 self._tail_early = True
-                self.comm.bucket_reduce_launch(self.arena.g_flat[b.start:self._tail_prefix[2]].data_ptr(),
-                                               self._tail_prefix[2] - b.start,
-                                               1.0 if self.pass_prescaled else 1.0 / self.world, self.arena.device)
+                if not self.dry_run_collectives:
+                    self.comm.bucket_reduce_launch(self.arena.g_flat[b.start:self._tail_prefix[2]].data_ptr(),
+                                                   self._tail_prefix[2] - b.start,
+                                                   1.0 if self.pass_prescaled else 1.0 / self.world, self.arena.device)
                 self._fused_adam(b.start, self._tail_prefix[2])
         if b.pending == 0:
             b.ready = True
@@ -321,7 +325,8 @@ class Reducer:
             if self._tail_early and self._tail_prefix is not None and b.index == self._tail_prefix[0]:
                 start = self._tail_prefix[2]                           # the prefix is already being reduced
                 t = self.arena.g_flat[start:b.end]
-            self.comm.bucket_reduce_launch(t.data_ptr(), t.numel(), premul, t.device)
+            if not self.dry_run_collectives:
+                self.comm.bucket_reduce_launch(t.data_ptr(), t.numel(), premul, t.device)
             self._fused_adam(start, b.end)
         else:
             t.mul_(1.0 / self.world)
