@@ -7,6 +7,7 @@
 #   launches             ncu launch list of a 3-step bench (after the same command ran clean without ncu)
 #   ncu REGEX N [args]   ncu --set full of the kernels matching REGEX (N launches) from scripts/kernel_bench.py
 #   kbench [args]        scripts/kernel_bench.py
+#   sweep N VAR v1 v2..  bench.py at N ranks once per value of the environment variable VAR (timed regions only)
 mkdir -p gpurun_out
 export PYTHONUNBUFFERED=1
 what=$1; shift
@@ -42,6 +43,24 @@ case "$what" in
     ;;
   kbench)
     timeout 900 python scripts/kernel_bench.py "$@" > gpurun_out/kernel_bench.log 2>&1; echo "kbench rc=$?"; tail -n 60 gpurun_out/kernel_bench.log
+    ;;
+  sweep)
+    # sweep N VAR v1 v2 ... : bench.py at N ranks (30 steps, timed regions only) for each value of environment variable VAR
+    n=$1; var=$2; shift 2
+    for v in "$@"; do
+      env $var=$v timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port 29512 \
+        bench.py --gpus $n --steps 30 --warmup 5 --no-extras > gpurun_out/sweep_${var}_$v.log 2>gpurun_out/sweep_${var}_$v.err
+      python - "$var=$v" gpurun_out/sweep_${var}_$v.log <<'PY'
+import json, sys
+try:
+    d = json.loads([l for l in open(sys.argv[2]) if l.startswith("{")][-1])
+    n = d.get("nccl") or {}
+    print(sys.argv[1], "ms/step %.3f" % d["ms_per_step"], "e2e %.3f" % d["e2e"]["ms_per_step"], "coll_ms %s busbw %s exposed %s dry %s" % (
+        n.get("collective_ms_per_step"), n.get("busbw_GBps"), n.get("exposed_comm_ms"), n.get("dry_step_ms")))
+except Exception as e:
+    print(sys.argv[1], "FAILED", e)
+PY
+    done
     ;;
   *) echo "unknown: $what"; exit 2;;
 esac

@@ -94,7 +94,9 @@ class Reducer:
             want = os.environ.get("B200DDP_ALLREDUCE", "own")
             in_arena = getattr(comm, "arena_mode", 0) >= 1 and any(t.data_ptr() == arena.g_flat.data_ptr()
                                                                     for _, t in getattr(comm, "_arenas", []))
-            if want in ("own", "peer") and in_arena and comm.set_algo("own", int(os.environ.get("B200DDP_AR_CTAS", "0"))):
+            big = os.environ.get("B200DDP_AR_BIG", "0") != "0"
+            ctas = int(os.environ.get("B200DDP_AR_CTAS", "8" if big else "64"))
+            if want in ("own", "peer") and in_arena and comm.set_algo("own", ctas):
                 self.algo = "own"
             elif want == "sum":
                 comm.set_algo("sum")
@@ -102,6 +104,11 @@ class Reducer:
             else:
                 comm.set_algo("ring")
             _comm_mod.reserve_sms_for_nccl(self.algo != "own")
+            if self.algo == "own" and big:       # 1024-thread CTAs own their SM: plan the compute grids around them
+                import ctypes
+                n = ctypes.c_int(148)
+                _lib.load().b200ddp_device_info(arena.device.index or 0, ctypes.byref(n), None, None)
+                _lib.load().b200ddp_set_sm_budget(max(16, n.value - ctas))
         self.pass_prescaled = False
         self.nonfinite_zero = nonfinite == "zero"
         self.prescale = False

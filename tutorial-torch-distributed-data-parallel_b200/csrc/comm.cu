@@ -133,6 +133,7 @@ struct Comm {
   bool have_devcomm = false;
   unsigned int epoch = 0;
   int ar_ctas = 64;
+  int ar_big = 0;            // 1: 1024-thread CTAs that own their SM (B200DDP_AR_BIG)
   int algo = 0;              // 0 = NCCL PreMulSum (ring), 1 = own kernel over peer memory, 2 = NCCL ncclSum on the registered arena
 };
 
@@ -247,6 +248,7 @@ int b200ddp_comm_create(void** out, const void* id_bytes, int rank, int nranks, 
     const int v = atoi(e);
     if (v >= 1 && v <= kPeerMaxCtas) c->ar_ctas = v;
   }
+  if (const char* e = getenv("B200DDP_AR_BIG")) c->ar_big = atoi(e) != 0;
   float inv = 1.0f / (float)nranks;
   r = g_nccl.RedOpCreatePreMulSum(&c->avg_op, &inv, ncclFloat32, ncclScalarHostImmediate, c->comm);
   c->have_avg_op = (r == ncclSuccess);
@@ -363,7 +365,7 @@ int b200ddp_bucket_reduce_launch(void* h, float* buf, long long n, float premul,
     a.epoch = c->epoch;
     c->epoch += 2;
     rc = peer_allreduce_launch(a, reinterpret_cast<char*>(buf) - reinterpret_cast<char*>(sb->ptr), n, premul, c->ar_ctas,
-                               c->comm_stream);
+                               c->ar_big, c->comm_stream);
   } else {
     rc = allreduce_on(c, buf, n, premul, c->comm_stream);
   }

@@ -25,6 +25,8 @@ struct PeerArgs {
 
 // In-place sum over ranks of buf[off_bytes .. off_bytes + 4 n) (n % 4 == 0, off_bytes % 16 == 0) of the symmetric
 // buffer described by a.data; every element is multiplied by `scale` after the sum (1/world = the mean).
-int peer_allreduce_launch(const PeerArgs& a, long long off_bytes, long long n, float scale, int ctas, cudaStream_t stream);
+// big_ctas = 0: `ctas` CTAs of 256 threads that co-reside with compute CTAs; 1: CTAs of 1024 threads that own their SM.
+int peer_allreduce_launch(const PeerArgs& a, long long off_bytes, long long n, float scale, int ctas, int big_ctas,
+                          cudaStream_t stream);
 
 }  // namespace b200

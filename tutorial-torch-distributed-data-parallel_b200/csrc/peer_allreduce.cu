@@ -34,8 +34,11 @@ namespace {
 // 14 warps x 128 registers (57,344 of an SM's 65,536 registers) and all of its shared / tensor memory, so what is left
 // is exactly 256 threads x 32 registers and no shared memory. The multimem kernel is built to that budget
 // (__launch_bounds__(256, 8)); many small CTAs then ride along on busy SMs and the convolution grids keep all 148 SMs.
-constexpr int kArThreads = 256;
-constexpr int kUnroll = 2;
+// A second shape does the opposite: few CTAs of 1024 threads x 4 loads in flight each (64 KB per SM), which fill the
+// register file and therefore own their SM like NCCL's channels do; the grid planners of the compute kernels then
+// leave those SMs out (b200ddp_set_sm_budget). Which one is faster is a measurement.
+constexpr int kArThreadsSmall = 256, kUnrollSmall = 2;
+constexpr int kArThreadsBig = 1024, kUnrollBig = 4;
 constexpr unsigned long long kWaitNs = 8000000000ull;
 
 __device__ __forceinline__ unsigned long long gtimer() {
@@ -97,8 +100,9 @@ __device__ __forceinline__ void peer_barrier(const PeerArgs& a, unsigned int epo
   __syncthreads();
 }
 
-template <bool MC>
-__global__ void __launch_bounds__(kArThreads, MC ? 8 : 4) peer_allreduce_kernel(PeerArgs a, long long off_bytes, long long n4, float scale) {
+template <bool MC, int kArThreads, int kUnroll>
+__global__ void __launch_bounds__(kArThreads, kArThreads == 256 ? (MC ? 8 : 4) : 1)
+peer_allreduce_kernel(PeerArgs a, long long off_bytes, long long n4, float scale) {
   peer_barrier(a, a.epoch + 1);                  // everybody's bucket is final (their producers ran before this kernel)
   const long long shard = (n4 + a.nranks - 1) / a.nranks;
   const long long lo = shard * a.rank, hi = lo + shard < n4 ? lo + shard : n4;
@@ -143,15 +147,21 @@ __global__ void __launch_bounds__(kArThreads, MC ? 8 : 4) peer_allreduce_kernel(
 
 }  // namespace
 
-int peer_allreduce_launch(const PeerArgs& a, long long off_bytes, long long n, float scale, int ctas, cudaStream_t stream) {
+int peer_allreduce_launch(const PeerArgs& a, long long off_bytes, long long n, float scale, int ctas, int big_ctas,
+                          cudaStream_t stream) {
   B200_CHECK_ARG(n >= 0 && (n & 3) == 0 && (off_bytes & 15) == 0, "peer_allreduce: range must be 16-byte aligned (n = %lld)", n);
   B200_CHECK_ARG(a.nranks >= 2 && a.nranks <= kPeerMaxRanks, "peer_allreduce: 2..%d ranks", kPeerMaxRanks);
   if (n == 0) return 0;
   if (ctas < 1) ctas = 1;
   if (ctas > kPeerMaxCtas) ctas = kPeerMaxCtas;
   const long long n4 = n >> 2;
-  if (a.data.mc) peer_allreduce_kernel<true><<<ctas, kArThreads, 0, stream>>>(a, off_bytes, n4, scale);
-  else peer_allreduce_kernel<false><<<ctas, kArThreads, 0, stream>>>(a, off_bytes, n4, scale);
+  if (big_ctas) {
+    if (a.data.mc) peer_allreduce_kernel<true, kArThreadsBig, kUnrollBig><<<ctas, kArThreadsBig, 0, stream>>>(a, off_bytes, n4, scale);
+    else peer_allreduce_kernel<false, kArThreadsBig, 1><<<ctas, kArThreadsBig, 0, stream>>>(a, off_bytes, n4, scale);
+  } else {
+    if (a.data.mc) peer_allreduce_kernel<true, kArThreadsSmall, kUnrollSmall><<<ctas, kArThreadsSmall, 0, stream>>>(a, off_bytes, n4, scale);
+    else peer_allreduce_kernel<false, kArThreadsSmall, 1><<<ctas, kArThreadsSmall, 0, stream>>>(a, off_bytes, n4, scale);
+  }
   B200_LAUNCH_OK();
   return 0;
 }
