@@ -811,6 +811,17 @@ def run_b200(args) -> None:
     assert torch.cuda.is_available(), "bench.py (own arm) needs a GPU: there is no CPU fallback"
     dev = torch.device("cuda", local)
     torch.cuda.set_device(dev)
+    pinned_cores = None
+    if world > 1 and os.environ.get("B200DDP_BENCH_PIN", "1") != "0" and hasattr(os, "sched_setaffinity"):
+        # one process per GPU, each on its own slice of the host cores: eight launch threads that migrate over and
+        # compete for the same cores show up as straggling ranks (every step waits for the slowest one)
+        try:
+            cores = sorted(os.sched_getaffinity(0))
+            per = max(1, len(cores) // world)
+            pinned_cores = cores[local * per:(local + 1) * per]
+            os.sched_setaffinity(0, pinned_cores)
+        except Exception:
+            pinned_cores = None
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
@@ -837,9 +848,8 @@ def run_b200(args) -> None:
 
     # ---- timed region: device-resident inputs ------------------------------------------------------------------------
     clocks = ClockSampler(local)
-    if rank == 0:
-        clocks.start()
-        time.sleep(0.02)
+    clocks.start()                # every rank samples its own GPU; rank 0's goes into "clocks", the rest into "ranks"
+    time.sleep(0.02)
     gc.collect()
     gc.disable()          # a collector pause inside a 0.1-0.5 s timed region is a multi-ms launch stall
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -861,12 +871,28 @@ def run_b200(args) -> None:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms_max = float(t)
     ms_step = ms_max / args.steps
+    # host side: how long the Python thread needs to ENQUEUE a step (8 steps from an idle device: the launch queue never
+    # fills, so this is pure host time). Close to ms_step = the step is launch-bound on this rank.
+    sync_all()
+    th0 = time.perf_counter()
+    for _ in range(8):
+        job.step_resident()
+    host_ms = 1e3 * (time.perf_counter() - th0) / 8
+    sync_all()
 
     # ---- timed regions: end to end -------------------------------------------------------------------------------------
     e2e = e2e_u8(job, args.steps, world, sync_all)
     e2e_f = e2e_fp32(job, min(args.steps, 50), world, sync_all)
     gc.enable()
-    clock_info = clocks.stop() if rank == 0 else None      # covers the resident and the end-to-end regions
+    clock_info = clocks.stop()                              # covers the resident and the end-to-end regions
+    rank_info = None
+    if world > 1:
+        mine = {"rank": rank, "resident_ms_per_step": ms / args.steps, "host_enqueue_ms_per_step": host_ms,
+                "sm_mhz": clock_info.get("sm_mhz"), "sm_min_mhz": clock_info.get("sm_min_mhz"),
+                "reasons": clock_info.get("reasons"), "cores": len(pinned_cores) if pinned_cores else None}
+        box = [None] * world
+        dist.all_gather_object(box, mine)
+        rank_info = box
     identical = replicas_identical(job, world) if world > 1 else None
 
     # ---- communication roofline, multi-GPU parity (untimed) ---------------------------------------------------------------
@@ -943,6 +969,8 @@ def run_b200(args) -> None:
             "roofline_groups": roofline_groups(kernels, ms_step, hbm_peak, tf32_peak),
             "kernels": kernels[:24],
             "final_loss": final_loss,
+            "host_enqueue_ms_per_step": host_ms,
+            "ranks": rank_info,
             "nccl": nccl,
             "parity_n": parity,
             "gpu_stock": stock,

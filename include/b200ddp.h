@@ -136,6 +136,38 @@ int b200ddp_gate_bias_bwd(const float* dy, const unsigned char* gate, float drop
 int b200ddp_softmax_ce(const float* logits, const long long* labels, float* loss, float* dlogits, int B, int C,
                        int* err_flag_dev, int device, void* stream);
 
+/* ---- T1: native step driver ------------------------------------------------------------------------------- */
+/* Replaces the layer-by-layer Python / autograd walk of `outputs = model(inputs)` and `loss.backward()` in reference
+ * train() (multi-GPU-training-torch.py:121,125) over torchvision AlexNet (alexnet.py:17-52, head of
+ * data_and_toy_model.py:44) by ONE call each, which enqueue the same kernels as the per-layer entry points above, in
+ * the same order with the same arguments (bit-identical results), out of one step-persistent workspace.
+ * Standard geometry only: x [B][3][224][224]; TF32 kernels. w / b: conv1..conv5, fc1, fc2, head (torch layouts).
+ * conv1_ktab: the k_order-0 offset table of b200ddp_conv2d_fwd for conv1 (Cin 3, 224x224, 11x11). */
+typedef struct b200ddp_alexnet_desc {
+  int B, hidden, num_classes;
+  float dropout_p;
+  const float* w[8];
+  const float* b[8];
+  const int* conv1_ktab;
+  void* workspace;             /* b200ddp_alexnet_workspace_bytes(B, hidden, num_classes) bytes, 256-byte aligned */
+  long long workspace_bytes;
+  int device;
+} b200ddp_alexnet_desc;
+typedef void (*b200ddp_ready_fn)(void* user, int group);
+long long b200ddp_alexnet_workspace_bytes(int B, int hidden, int num_classes);
+int b200ddp_alexnet_plan_create(void** plan_out, const b200ddp_alexnet_desc* desc);
+int b200ddp_alexnet_plan_destroy(void* plan);
+/* train != 0 keeps gates / argmax codes for backward and applies dropout (seed0: classifier.0, seed1: classifier.1);
+ * out = logits [B][classes], or the head's input [B][hidden] when stop_at_hidden != 0 (evaluate()). */
+int b200ddp_alexnet_forward(void* plan, const float* x, float* out, int train, unsigned long long seed0,
+                            unsigned long long seed1, int stop_at_hidden, void* stream);
+/* Backward of the last training forward (x = its input). dw[i] / db[i] are WRITTEN. ready(user, g) is called on the
+ * host once group g's gradients are enqueued on `stream` (0 head+fc2, 1 fc1, 2 conv5..conv2, 3 conv1): the DDP
+ * reducer launches its bucket all-reduce from there. use_side_stream: weight gradients of conv5..conv2 on the plan's
+ * own stream (joined before group 2 is reported). */
+int b200ddp_alexnet_backward(void* plan, const float* x, const float* dlogits, float* const* dw, float* const* db,
+                             float dropout_p_used, b200ddp_ready_fn ready, void* user, int use_side_stream, void* stream);
+
 /* ---- f1: evaluate() ------------------------------------------------------------------------------------- */
 /* Replaces, per test batch of reference evaluate() (multi-GPU-training-torch.py:136-153, -accelerate.py:60-75), the
  * head Linear (classifier.6) + criterion + loss.item() + torch.max(outputs, 1) + (predicted == labels).sum().item():

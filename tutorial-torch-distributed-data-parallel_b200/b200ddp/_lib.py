@@ -31,6 +31,15 @@ class WeightPrepJob(ctypes.Structure):
                 ("ld_out", c_longlong), ("mode", c_int)]
 
 
+class AlexNetDesc(ctypes.Structure):
+    """b200ddp_alexnet_desc (include/b200ddp.h)."""
+    _fields_ = [("B", c_int), ("hidden", c_int), ("num_classes", c_int), ("dropout_p", c_float),
+                ("w", c_void_p * 8), ("b", c_void_p * 8), ("conv1_ktab", c_void_p), ("workspace", c_void_p),
+                ("workspace_bytes", c_longlong), ("device", c_int)]
+
+
+READY_FN = ctypes.CFUNCTYPE(None, c_void_p, c_int)      # b200ddp_ready_fn
+
 _PROTOS = {
     "b200ddp_last_error": (c_char_p, []),
     "b200ddp_version": (c_int, []),
@@ -71,6 +80,11 @@ _PROTOS = {
     "b200ddp_softmax_ce": (c_int, [_P, _P, _P, _P, c_int, c_int, _P, c_int, _P]),
     "b200ddp_conv2d_fwd": (c_int, [_P, _P, c_longlong, _P, _P, _P, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int,
                                    c_int, c_int, c_int, c_int, _P]),
+    "b200ddp_alexnet_workspace_bytes": (c_longlong, [c_int, c_int, c_int]),
+    "b200ddp_alexnet_plan_create": (c_int, [POINTER(c_void_p), POINTER(AlexNetDesc)]),
+    "b200ddp_alexnet_plan_destroy": (c_int, [_P]),
+    "b200ddp_alexnet_forward": (c_int, [_P, _P, _P, c_int, c_ulonglong, c_ulonglong, c_int, _P]),
+    "b200ddp_alexnet_backward": (c_int, [_P, _P, _P, POINTER(c_void_p), POINTER(c_void_p), c_float, READY_FN, _P, c_int, _P]),
     "b200ddp_eval_scratch_bytes": (c_longlong, [c_int]),
     "b200ddp_head_eval": (c_int, [_P, _P, _P, _P, _P, c_int, c_int, c_int, _P, _P, c_longlong, c_int, _P]),
     "b200ddp_logits_eval": (c_int, [_P, _P, c_int, c_int, _P, _P, c_longlong, c_int, _P]),

@@ -25,6 +25,7 @@ from __future__ import annotations
 import torch
 from torch import nn
 
+from . import engine
 from . import nn as bnn
 
 
@@ -67,6 +68,13 @@ class AlexNet(nn.Module):
     def forward_hidden(self, x: torch.Tensor) -> torch.Tensor:
         """Everything up to (not including) the 10-class head: the [B, hidden] input of classifier.6.
         `b200ddp.evaluate` feeds it to the fused head + metrics kernel."""
+        if not torch.is_grad_enabled() and engine.applicable(self, x):
+            out = engine.run(self, x, stop_at_hidden=True)      # one native call (csrc/engine.cu)
+            if out is not None:
+                return out
+        return self._hidden_by_modules(x)
+
+    def _hidden_by_modules(self, x: torch.Tensor) -> torch.Tensor:
         convs = [m for m in self.features if isinstance(m, bnn.Conv2d)]
         if convs and x.is_cuda:
             bnn.prepare_conv_weights(convs, first_needs_dgrad=x.requires_grad)     # all GEMM weight copies, one launch
@@ -79,7 +87,11 @@ class AlexNet(nn.Module):
         return x
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
-        return self.classifier[-1](self.forward_hidden(x))
+        if engine.applicable(self, x):
+            out = engine.run(self, x)           # whole forward (and later backward) as one native call each
+            if out is not None:
+                return out
+        return self.classifier[-1](self._hidden_by_modules(x))
 
 
 def fuse_bn_relu(model: nn.Module) -> nn.Module:

@@ -95,7 +95,9 @@ class Reducer:
             in_arena = getattr(comm, "arena_mode", 0) >= 1 and any(t.data_ptr() == arena.g_flat.data_ptr()
                                                                     for _, t in getattr(comm, "_arenas", []))
             big = os.environ.get("B200DDP_AR_BIG", "0") != "0"
-            ctas = int(os.environ.get("B200DDP_AR_CTAS", "8" if big else "64"))
+            # measured (profiles/r02_allreduce_sweep.md): small CTAs, 64 of them at 2 ranks (each rank moves half of
+            # the bucket through its SMs), 16 at 4+ ranks (an eighth: fewer CTAs disturb the convolutions less)
+            ctas = int(os.environ.get("B200DDP_AR_CTAS", "8" if big else ("64" if self.world < 4 else "16")))
             if want in ("own", "peer") and in_arena and comm.set_algo("own", ctas):
                 self.algo = "own"
             elif want == "sum":
@@ -145,6 +147,7 @@ class Reducer:
                 self.bucket_of[i] = b.index
         self.next_bucket = 0
         self._callback_queued = False
+        self._native_done = set()
         self._ready_order: List[int] = []
         self.first_ready_order: Optional[List[int]] = None
         # Early launch inside the LAST bucket: its final members (the first layer's weight and bias) become ready only
@@ -236,6 +239,7 @@ class Reducer:
         self.next_bucket = 0
         self._callback_queued = False
         self._ready_order = []
+        self._native_done = set()
         self._tail_early = False
         self._tail_prefix_pending = len(self._tail_prefix[1]) if self._tail_prefix is not None else 0
         # fused optimizer: only for a backward pass that starts from empty gradients (no accumulation pending)
@@ -247,8 +251,17 @@ class Reducer:
             self._fused_t = opt._next_step_count(self.arena)
         self.fresh_grads = False
 
-    def _on_grad_ready(self, i: int, param) -> None:
+    def mark_ready_native(self, indices) -> None:
+        """Called from inside the native backward (b200ddp.engine): the gradients of these arena parameters have just been
+        enqueued, written straight into their arena slices. Their autograd hooks, which fire later in the same backward
+        pass, are then ignored."""
+        for i in indices:
+            self._on_grad_ready(i, None, native=True)
+
+    def _on_grad_ready(self, i: int, param, native: bool = False) -> None:
         if not self.require_sync:
+            return
+        if self._callback_queued and i in self._native_done:
             return
         if not self._callback_queued:
             self._reset()
@@ -258,7 +271,9 @@ class Reducer:
             Variable._execution_engine.queue_callback(self._finalize)
         self._ready_order.append(i)
         arena = self.arena
-        if not arena.grad_in_arena(i):
+        if native:
+            self._native_done.add(i)
+        elif not arena.grad_in_arena(i):
             # gradient was produced outside the arena (e.g. by a cuDNN wgrad): pack it into its slice
             g = param.grad
             view = arena.grad_view(i)
