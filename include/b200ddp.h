@@ -103,6 +103,9 @@ int b200ddp_comm_arena_alloc(void* handle, long long nbytes, void** ptr_out, int
  * `ctas` CTAs of 256 threads, <= 256; buffers outside an arena fall back to 0), 2 NCCL ncclSum on pre-scaled data.
  * Returns 1 if the peer path is available, 0 if not, < 0 on a bad argument. Same value on every rank. */
 int b200ddp_comm_set_algo(void* handle, int algo, int ctas);
+/* CTA shape of that kernel: 0 = 256 threads x 32 registers (fits beside a running convolution CTA), 1 = 1024 threads
+ * (owns its SM; leave `ctas` SMs out of the compute grids with b200ddp_set_sm_budget). */
+int b200ddp_comm_set_cta_shape(void* handle, int big);
 /* Device time of each bucket collective of the last joined backward pass (for the NVLink roofline: busBW =
  * 4 n * 2 (ws-1)/ws / t). set_timing(1) first; synchronise before reading. Returns the number of entries. */
 int b200ddp_comm_set_timing(void* handle, int on);

@@ -336,6 +336,7 @@ def case_own_allreduce_known_values(rank, world, out_dir, dev):
     """R4: the library's own all-reduce kernel over the registered arena (multimem / peer loads), through the C ABI,
     against exact expectations and against torch.distributed's NCCL all-reduce: whole arena, ranges at offsets, sizes
     that do not divide by the world size, many launches in a row (flag epochs), several CTA counts."""
+    from b200ddp import _lib
     from b200ddp.comm import get_comm
     comm = get_comm(dev, None)
     n = 3 * 1024 * 1024 + 64 * 5
@@ -350,6 +351,7 @@ def case_own_allreduce_known_values(rank, world, out_dir, dev):
     for it, (start, cnt, ctas) in enumerate([(0, n, 64), (64, 4096, 8), (1 << 20, (1 << 20) + 64 * 3, 200), (0, n, 1),
                                              (n - 64, 64, 16)] * 3):
         comm.set_algo("own" if peer else "ring", ctas)
+        _lib.load().b200ddp_comm_set_cta_shape(comm.handle, it % 2)       # both CTA shapes of the kernel
         buf.copy_((idx % 1000) + 7.0 * (rank + 1) + it)                 # small integers: sums are exact in fp32
         want = buf.clone()
         seg = want[start:start + cnt].clone()

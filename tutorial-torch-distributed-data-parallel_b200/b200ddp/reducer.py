@@ -94,12 +94,19 @@ class Reducer:
             want = os.environ.get("B200DDP_ALLREDUCE", "own")
             in_arena = getattr(comm, "arena_mode", 0) >= 1 and any(t.data_ptr() == arena.g_flat.data_ptr()
                                                                     for _, t in getattr(comm, "_arenas", []))
-            big = os.environ.get("B200DDP_AR_BIG", "0") != "0"
-            # measured (profiles/r02_allreduce_sweep.md): small CTAs, 64 of them at 2 ranks (each rank moves half of
-            # the bucket through its SMs), 16 at 4+ ranks (an eighth: fewer CTAs disturb the convolutions less)
-            ctas = int(os.environ.get("B200DDP_AR_CTAS", "8" if big else ("64" if self.world < 4 else "16")))
+            # Shape of the own kernel, measured on 2 and 8 B200s (profiles/r02_allreduce_sweep.md): a few 1024-thread CTAs
+            # that own their SM (the compute grids are planned around them) beat many small co-resident ones for the step
+            # time, although the small ones reach a higher bus bandwidth: 8 CTAs at 2 ranks (each rank moves half of every
+            # bucket through its SMs), 4 at 8 ranks (an eighth).
+            big = os.environ.get("B200DDP_AR_BIG", "1") != "0"
+            if big:
+                dflt = 8 if self.world <= 2 else (6 if self.world <= 4 else 4)
+            else:
+                dflt = 64 if self.world < 4 else (32 if arena.numel * 4 > (400 << 20) else 16)
+            ctas = int(os.environ.get("B200DDP_AR_CTAS", str(dflt)))
             if want in ("own", "peer") and in_arena and comm.set_algo("own", ctas):
                 self.algo = "own"
+                _lib.load().b200ddp_comm_set_cta_shape(comm.handle, 1 if big else 0)
             elif want == "sum":
                 comm.set_algo("sum")
                 self.algo = "sum"
@@ -111,6 +118,7 @@ class Reducer:
                 n = ctypes.c_int(148)
                 _lib.load().b200ddp_device_info(arena.device.index or 0, ctypes.byref(n), None, None)
                 _lib.load().b200ddp_set_sm_budget(max(16, n.value - ctas))
+        self._chunk_elems = max(1, int(os.environ.get("B200DDP_AR_CHUNK_MB", "64"))) << 18      # MB -> fp32 elements
         self.pass_prescaled = False
         self.nonfinite_zero = nonfinite == "zero"
         self.prescale = False
@@ -347,9 +355,17 @@ class Reducer:
             if self._tail_early and self._tail_prefix is not None and b.index == self._tail_prefix[0]:
                 start = self._tail_prefix[2]                           # the prefix is already being reduced
                 t = self.arena.g_flat[start:b.end]
-            if not self.dry_run_collectives:
-                self.comm.bucket_reduce_launch(t.data_ptr(), t.numel(), premul, t.device)
-            self._fused_adam(start, b.end)
+            # Large buckets go out in chunks: the optimizer launch of chunk k (it waits for that chunk's collective only)
+            # then overlaps the collective of chunk k+1, and reads the averaged gradients while they are still in L2.
+            # Without this the Adam pass over a 300 MB bucket can only start when its whole all-reduce has finished.
+            chunk = self._chunk_elems if self._fused_now is not None else (b.end - start)
+            s = start
+            while s < b.end:
+                e = min(s + chunk, b.end)
+                if not self.dry_run_collectives:
+                    self.comm.bucket_reduce_launch(self.arena.g_flat.data_ptr() + 4 * s, e - s, premul, t.device)
+                self._fused_adam(s, e)
+                s = e
         else:
             t.mul_(1.0 / self.world)
             b.work = dist.all_reduce(t, group=self.pg, async_op=True)

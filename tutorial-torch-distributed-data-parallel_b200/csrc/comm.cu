@@ -445,6 +445,13 @@ int b200ddp_comm_set_algo(void* h, int algo, int ctas) {
   return c->peer_ok ? 1 : 0;
 }
 
+// CTA shape of the own all-reduce kernel: 0 = 256 threads (co-resident with compute CTAs), 1 = 1024 threads (owns its SM).
+int b200ddp_comm_set_cta_shape(void* h, int big) {
+  if (!h) return -1;
+  reinterpret_cast<Comm*>(h)->ar_big = big != 0;
+  return 0;
+}
+
 // Per-bucket device time of the collectives of the most recently JOINED backward pass (timing must be on and the
 // caller must have synchronised the device). Returns the number of entries written.
 int b200ddp_comm_set_timing(void* h, int on) {
