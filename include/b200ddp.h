@@ -152,6 +152,7 @@ typedef struct b200ddp_alexnet_desc {
   const float* w[8];
   const float* b[8];
   const int* conv1_ktab;
+  int conv1_order;             /* k_order of the first layer's forward: 0 (offset table) or 2 (slab kernel, conv1.cu) */
   void* workspace;             /* b200ddp_alexnet_workspace_bytes(B, hidden, num_classes) bytes, 256-byte aligned */
   long long workspace_bytes;
   int device;
@@ -225,6 +226,8 @@ int b200ddp_conv2d_dgrad_fp32(const float* dy, const float* w, float* dx, int Nb
                               int KW, int stride, int pad, int device, void* stream);
 int b200ddp_conv2d_wgrad_fp32(const float* x, const float* dy, float* dw, int Nb, int Cin, int H, int W, int Cout, int KH,
                               int KW, int stride, int pad, int device, void* stream);
+/* k_order 2 of b200ddp_conv2d_fwd = the first layer's own kernel (conv1.cu; Cin 3, 11x11, stride 4, Cout 64, W + 2 pad <=
+ * 256): wmat from weight_prep mode 5, out[co][ci*136 + kh*12 + kw] = w[co][ci][kh][kw], zero elsewhere, ld_out >= 416. */
 /* mode 0: out[co][0..ld_out) = w[co][:] zero padded; mode 1: flipped / transposed weights for dgrad,
  * out[ci][co*KH*KW + (KH-1-kh)*KW + (KW-1-kw)] = w[co][ci][kh][kw], row stride ld_out; modes 2 / 3: the same two
  * matrices with the reduction index in channel-block-major order (k_order 1). */

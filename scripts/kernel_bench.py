@@ -181,6 +181,9 @@ for (Cin, H, Cout, K, s_, p_, tag) in ((3, 224, 64, 11, 4, 2, "conv1"), (64, 27,
     bias = conv.bias.detach()
     yb_ = 4.0 * (xin.numel() + B * Cout * OH * OH + w.numel())
     timeit(f"conv2d_fwd {tag} (k_order {ko})", lambda: bnn.conv2d_forward_raw(xin, wmat, ldw, bias, Cout, K, K, s_, p_, False, ko), yb_, fl)
+    if bnn._use_slab(Cin, K, K, s_, Cout, H, p_):
+        wm5, ld5 = bnn.conv_weight_matrix(w, 5)
+        timeit(f"conv2d_fwd {tag} (k_order 2, slab kernel)", lambda: bnn.conv2d_forward_raw(xin, wm5, ld5, bias, Cout, K, K, s_, p_, False, 2), yb_, fl)
     dyc = torch.randn(B, Cout, OH, OH, device=DEV)
     dwc = torch.empty_like(w)
     ktab = bnn._conv_tables(DEV, Cin, H, H, K, K) if ko == 0 else None

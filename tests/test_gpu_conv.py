@@ -277,3 +277,34 @@ def test_conv_strict_fp32_matches_float64(layer):
     assert _err(x.grad, x64.grad) < 2e-6          # stride 4 included: the strict dgrad has no stride limit
     assert _err(conv.weight.grad, w64.grad) < 2e-6
     assert _err(conv.bias.grad, b64.grad) < 1e-5
+
+
+def test_conv1_generic_kernel_still_matches_float64(monkeypatch):
+    """The first layer through the generic implicit-GEMM kernel (k_order 0, offset table) instead of its own slab kernel."""
+    monkeypatch.setenv("B200DDP_CONV1_SLAB", "0")
+    torch.manual_seed(3)
+    x = torch.randn(5, 3, 224, 224, device=DEV)
+    conv = bnn.Conv2d(3, 64, 11, stride=4, padding=2).to(DEV)
+    y = conv(x)
+    ref = torch.nn.functional.conv2d(x.double(), conv.weight.double(), conv.bias.double(), stride=4, padding=2)
+    assert _err(y, ref) < TOL
+
+
+def test_conv1_slab_kernel_edges_and_other_widths():
+    """conv1.cu: image borders (TMA zero fill), the last single-row tile, non-finite inputs stay local, other input sizes."""
+    torch.manual_seed(4)
+    for (b, hw) in [(3, 224), (2, 160), (1, 67 * 4 - 4 + 8)]:
+        x = torch.randn(b, 3, hw, hw, device=DEV)
+        conv = bnn.Conv2d(3, 64, 11, stride=4, padding=2).to(DEV)
+        y = conv(x)
+        ref = torch.nn.functional.conv2d(x.double(), conv.weight.double(), conv.bias.double(), stride=4, padding=2)
+        assert y.shape == ref.shape and _err(y, ref) < TOL, (b, hw)
+    # an infinite pixel must only reach the outputs whose 11x11 window really contains it (the kernel reads a 12th tap)
+    x = torch.zeros(1, 3, 224, 224, device=DEV)
+    x[0, 1, 100, 109] = float("inf")
+    conv = bnn.Conv2d(3, 64, 11, stride=4, padding=2).to(DEV)
+    with torch.no_grad():
+        conv.weight.abs_().add_(0.1)
+    y = conv(x)
+    ref = torch.nn.functional.conv2d(x, conv.weight, conv.bias, stride=4, padding=2)
+    assert torch.equal(torch.isfinite(y), torch.isfinite(ref))

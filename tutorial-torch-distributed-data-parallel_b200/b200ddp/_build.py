@@ -14,7 +14,7 @@ REPO = os.path.dirname(os.path.dirname(PKG_DIR))
 LIB_PATH = os.path.join(PKG_DIR, "libb200ddp.so")
 OBJ_DIR = os.path.join(CSRC, "build")
 
-SOURCES = ["abi.cu", "adam.cu", "reduce.cu", "comm.cu", "peer_allreduce.cu", "plan.cu", "linear.cu", "gemm_tf32.cu", "conv.cu", "conv_fp32.cu", "loss.cu",
+SOURCES = ["abi.cu", "adam.cu", "reduce.cu", "comm.cu", "peer_allreduce.cu", "plan.cu", "linear.cu", "gemm_tf32.cu", "conv.cu", "conv1.cu", "conv_fp32.cu", "loss.cu",
            "pool.cu", "bn.cu", "eval.cu", "transform.cu", "engine.cu"]
 
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",

@@ -34,7 +34,7 @@ class WeightPrepJob(ctypes.Structure):
 class AlexNetDesc(ctypes.Structure):
     """b200ddp_alexnet_desc (include/b200ddp.h)."""
     _fields_ = [("B", c_int), ("hidden", c_int), ("num_classes", c_int), ("dropout_p", c_float),
-                ("w", c_void_p * 8), ("b", c_void_p * 8), ("conv1_ktab", c_void_p), ("workspace", c_void_p),
+                ("w", c_void_p * 8), ("b", c_void_p * 8), ("conv1_ktab", c_void_p), ("conv1_order", c_int), ("workspace", c_void_p),
                 ("workspace_bytes", c_longlong), ("device", c_int)]
 
 

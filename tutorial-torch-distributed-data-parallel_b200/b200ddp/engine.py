@@ -55,6 +55,8 @@ class StepPlan:
             d.w[i] = m.weight.data_ptr()
             d.b[i] = m.bias.data_ptr()
         d.conv1_ktab = self.ktab.data_ptr()
+        self.conv1_order = 2 if bnn._use_slab(3, 11, 11, 4, 64, 224, 2) else 0
+        d.conv1_order = self.conv1_order
         d.workspace, d.workspace_bytes = base, nbytes
         d.device = dev.index if dev.index is not None else torch.cuda.current_device()
         self.signature = tuple(p.data_ptr() for p in self.params)
@@ -106,7 +108,8 @@ def plan_for(model, batch: int) -> Optional[StepPlan]:
     plans = model.__dict__.setdefault("_engine_plans", {})
     plan = plans.get(batch)
     if plan is not None:
-        if plan.signature != tuple(p.data_ptr() for p in plan.params) or plan.dropout != float(plan.layers[5].dropout):
+        if (plan.signature != tuple(p.data_ptr() for p in plan.params) or plan.dropout != float(plan.layers[5].dropout)
+                or plan.conv1_order != (2 if bnn._use_slab(3, 11, 11, 4, 64, 224, 2) else 0)):
             plan = None                                   # parameters were re-pointed (DDP wrap, .to()): rebuild
     if plan is None:
         if len(plans) >= 3:                               # full batch, ragged last batch, evaluation batch

@@ -77,7 +77,7 @@ class AlexNet(nn.Module):
     def _hidden_by_modules(self, x: torch.Tensor) -> torch.Tensor:
         convs = [m for m in self.features if isinstance(m, bnn.Conv2d)]
         if convs and x.is_cuda:
-            bnn.prepare_conv_weights(convs, first_needs_dgrad=x.requires_grad)     # all GEMM weight copies, one launch
+            bnn.prepare_conv_weights(convs, first_needs_dgrad=x.requires_grad, in_width=x.shape[3])   # all GEMM weight copies, one launch
         x = self.features(x)
         if x.shape[-2:] != (6, 6):
             x = self.avgpool(x)

@@ -179,6 +179,17 @@ def _k_order(cin: int) -> int:
     return 1 if cin % 32 == 0 else 0
 
 
+def _use_slab(Cin: int, KH: int, KW: int, stride: int, Cout: int, W: int, pad: int) -> bool:
+    """k_order 2: the first layer's own kernel (csrc/conv1.cu) - image slab staged in shared memory by TMA."""
+    if os.environ.get("B200DDP_CONV1_SLAB", "1") == "0":
+        return False
+    return (Cin, KH, KW, stride, Cout, pad) == (3, 11, 11, 4, 64, 2) and W % 4 == 0 and 11 <= W <= 240
+
+
+def _slab_ld(Cin: int, KH: int) -> int:
+    return (Cin * ((KH * 12 + 7) // 8 * 8) + 31) // 32 * 32
+
+
 def conv2d_forward_raw(x, wmat, ldw, bias, Cout, KH, KW, stride, pad, relu, k_order):
     """y = conv(x, wmat) through b200ddp_conv2d_fwd; x [N,Cin,H,W] contiguous fp32 CUDA; wmat in `k_order`."""
     L = _lib.load()
@@ -197,7 +208,9 @@ def conv_weight_matrix(w, mode: int):
     forward weights [Cout][K]; 1 / 3 flipped, transposed dgrad weights [Cin][Cout*KH*KW]."""
     L = _lib.load()
     Cout, Cin, KH, KW = w.shape
-    if mode in (0, 2):
+    if mode == 5:
+        rows, ld = Cout, _slab_ld(Cin, KH)
+    elif mode in (0, 2):
         rows, ld = Cout, ((Cin * KH * KW + 31) // 32 * 32 if mode == 0 else Cin * KH * KW)
     else:
         rows, ld = Cin, Cout * KH * KW
@@ -322,9 +335,12 @@ class _Conv2dFn(torch.autograd.Function):
         elif prepared is not None:      # GEMM copies made by prepare_conv_weights() for this forward/backward pair
             wmat, ldw = prepared["fwd"]
             ctx.dgrad_weights = prepared.get("dgrad")
-            y = conv2d_forward_raw(x, wmat, ldw, bias, Cout, KH, KW, stride, pad, relu and not pool, ko)
+            y = conv2d_forward_raw(x, wmat, ldw, bias, Cout, KH, KW, stride, pad, relu and not pool, prepared.get("ko", ko))
         else:
-            if ko == 1:
+            if _use_slab(Cin, KH, KW, stride, Cout, x.shape[3], pad):
+                wmat, ldw = conv_weight_matrix(w, 5)
+                ko = 2
+            elif ko == 1:
                 wmat, ldw = conv_weight_matrix(w, 2)
             elif K % 4 == 0 and w.data_ptr() % 16 == 0:
                 wmat, ldw = w, K
@@ -467,7 +483,7 @@ class Conv2d(nn.Conv2d):
         self._prepared = None                     # set by prepare_conv_weights(), consumed by the next forward
         self._prep_bufs = {}
 
-    def _prep_jobs(self, need_dgrad: bool):
+    def _prep_jobs(self, need_dgrad: bool, in_width=None):
         """(jobs, prepared) for prepare_conv_weights: GEMM copies of the weights for forward and, optionally, dgrad."""
         w = self.weight.data
         Cout, Cin, KH, KW = w.shape
@@ -486,6 +502,11 @@ class Conv2d(nn.Conv2d):
             out = buf("fwd_s2d", Cout, ld)
             jobs.append((w, out, 4 | (S << 8), ld))
             prepared["fwd_s2d"] = (out, ld)
+        elif in_width is not None and _use_slab(Cin, KH, KW, self.stride[0], Cout, in_width, self.padding[0]):
+            ld = _slab_ld(Cin, KH)
+            out = buf("fwd", Cout, ld)
+            jobs.append((w, out, 5, ld))
+            prepared["fwd"], prepared["ko"] = (out, ld), 2
         elif _k_order(Cin) == 1:
             out = buf("fwd", Cout, K)
             jobs.append((w, out, 2, K))
@@ -510,7 +531,7 @@ class Conv2d(nn.Conv2d):
                                self.mode)
 
 
-def prepare_conv_weights(convs, first_needs_dgrad: bool = False) -> None:
+def prepare_conv_weights(convs, first_needs_dgrad: bool = False, in_width=None) -> None:
     """One launch (b200ddp_conv2d_weight_prep_multi) that writes the GEMM copies of the weights of every Conv2d in
     `convs` (in network order) for the forward pass that follows and its backward: forward copies for all layers,
     dgrad copies for all but the first (whose input needs no gradient unless `first_needs_dgrad`)."""
@@ -524,7 +545,8 @@ def prepare_conv_weights(convs, first_needs_dgrad: bool = False) -> None:
                 or conv.mode == MODE_FP32):
             conv._prepared = None
             continue
-        j, prepared = conv._prep_jobs(need_dgrad=torch.is_grad_enabled() and (i > 0 or first_needs_dgrad))
+        j, prepared = conv._prep_jobs(need_dgrad=torch.is_grad_enabled() and (i > 0 or first_needs_dgrad),
+                                      in_width=in_width if i == 0 else None)
         jobs += j
         conv._prepared = prepared
     if not jobs:

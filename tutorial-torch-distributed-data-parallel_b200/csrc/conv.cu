@@ -607,6 +607,19 @@ __device__ __forceinline__ void weight_prep_body(const float* __restrict__ w, fl
     }
     return;
   }
+  if (mode == 5) {
+    // first-layer slab order (conv1.cu): k' = ci * SC + kh * 12 + kw, SC = KH * 12 rounded up to a multiple of 8; zero elsewhere
+    const int SC = (KH * 12 + 7) / 8 * 8, ld = (int)ld_out;
+    const int total = Cout * ld;
+    for (int i = (int)first; i < total; i += (int)stride) {
+      const int co = i / ld, k = i - co * ld;
+      const int ci = k / SC, r = k - ci * SC, kh = r / 12, kw = r - kh * 12;
+      float v = 0.f;
+      if (ci < Cin && kh < KH && kw < KW) v = __ldg(w + (((long long)co * Cin + ci) * KH + kh) * KW + kw);
+      out[i] = v;
+    }
+    return;
+  }
   if (mode == 0) {
     const int K = Cin * KHW;
     const int total = Cout * (int)ld_out, ld = (int)ld_out;       // host guarantees < 2^31
@@ -842,7 +855,12 @@ int b200ddp_conv2d_fwd(const float* x, const float* wmat, long long ldw, const f
                        int k_order, int Nb, int Cin, int H, int W, int Cout, int KH, int KW, int stride, int pad, int relu,
                        int device, void* stream) {
   B200_CHECK_ARG(x && wmat && y, "conv2d_fwd: null argument");
-  B200_CHECK_ARG(k_order == 0 || k_order == 1, "conv2d_fwd: k_order must be 0 (ci,kh,kw) or 1 (ci/32,kh,kw,ci%%32)");
+  if (k_order == 2) {       // the first layer's own kernel (conv1.cu): image slab staged in shared memory by TMA
+    B200_CHECK_ARG(Nb > 0 && H > 0 && W > 0, "conv2d_fwd: bad shape");
+    B200_DEVICE(device);
+    return conv1_fwd_launch(x, wmat, ldw, bias, y, Nb, Cin, H, W, Cout, KH, KW, stride, pad, relu, as_stream(stream));
+  }
+  B200_CHECK_ARG(k_order == 0 || k_order == 1, "conv2d_fwd: k_order must be 0 (ci,kh,kw), 1 (ci/32,kh,kw,ci%%32) or 2 (first layer)");
   B200_CHECK_ARG(k_order == 1 || (ktab && ((uintptr_t)ktab & 7) == 0), "conv2d_fwd: k_order 0 needs an 8-byte aligned ktab");
   B200_CHECK_ARG(k_order == 0 || (Cin % 32) == 0, "conv2d_fwd: k_order 1 needs Cin %% 32 == 0 (Cin = %d)", Cin);
   B200_CHECK_ARG(k_order == 1 || (KH <= 15 && KW <= 15), "conv2d_fwd: k_order 0 supports kernel sizes up to 15 (got %dx%d)", KH, KW);
@@ -993,7 +1011,11 @@ int b200ddp_conv2d_wgrad(const float* x, const float* dy, float* dw, const int* 
 
 static int check_prep_mode(int Cout, int Cin, int KH, int KW, long long ld_out, int mode, const char* who) {
   const int m = mode & 0xff, S = mode >> 8;
-  B200_CHECK_ARG(m >= 0 && m <= 4 && (m == 4 || S == 0), "%s: mode must be 0..3 or 4 | S << 8 (got %d)", who, mode);
+  B200_CHECK_ARG(m >= 0 && m <= 5 && (m == 4 || S == 0), "%s: mode must be 0..3, 4 | S << 8 or 5 (got %d)", who, mode);
+  if (m == 5) {
+    B200_CHECK_ARG(KW <= 12 && ld_out >= (long long)Cin * ((KH * 12 + 7) / 8 * 8), "%s: mode 5 needs KW <= 12 and ld_out >= Cin * roundup8(12 KH)", who);
+    return 0;
+  }
   if (m == 4) {
     B200_CHECK_ARG(S >= 2 && S <= 8 && Cin * S * S <= 64, "%s: space-to-depth needs 2 <= S <= 8 and Cin*S*S <= 64", who);
     B200_CHECK_ARG(ld_out >= 64LL * ((KH + S - 1) / S) * ((KW + S - 1) / S), "%s: ld_out too small", who);
@@ -1014,7 +1036,7 @@ static long long prep_total(int Cout, int Cin, int KH, int KW, long long ld_out,
     const int S = mode >> 8;
     return (long long)Cout * 64 * ((KH + S - 1) / S) * ((KW + S - 1) / S);
   }
-  return mode == 0 ? (long long)Cout * ld_out : (long long)Cout * Cin * KH * KW;
+  return (mode == 0 || mode == 5) ? (long long)Cout * ld_out : (long long)Cout * Cin * KH * KW;
 }
 
 int b200ddp_conv2d_weight_prep(const float* w, float* out, int Cout, int Cin, int KH, int KW, long long ld_out, int mode,

@@ -82,6 +82,7 @@ size_t layout(Plan& P, void* base) {
     const ConvGeo& g = kConv[l];
     const long long K = (long long)g.Cin * g.K * g.K;
     P.ldf[l] = (g.Cin % 32 == 0) ? K : (K + 31) / 32 * 32;
+    if (l == 0 && d.conv1_order == 2) P.ldf[l] = (g.Cin * ((g.K * 12 + 7) / 8 * 8) + 31) / 32 * 32;      // slab order (conv1.cu)
     P.wf[l] = c.take<float>((size_t)g.Cout * P.ldf[l]);
     P.ldd[l] = (long long)g.Cout * g.K * g.K;
     P.wd[l] = l > 0 ? c.take<float>((size_t)g.Cin * P.ldd[l]) : nullptr;
@@ -143,8 +144,9 @@ extern "C" {
 
 long long b200ddp_alexnet_workspace_bytes(int B, int hidden, int num_classes) {
   if (B <= 0 || hidden <= 0 || num_classes <= 0) return -1;
-  Plan P;
+  Plan P{};
   P.d.B = B; P.d.hidden = hidden; P.d.num_classes = num_classes;
+  P.d.conv1_order = 2;            // the larger of the two first-layer weight layouts
   return (long long)layout(P, nullptr);
 }
 
@@ -203,7 +205,7 @@ int b200ddp_alexnet_forward(void* plan, const float* x, float* out, int train, u
   int nj = 0;
   for (int l = 0; l < 5; ++l) {
     const ConvGeo& g = kConv[l];
-    jobs[nj++] = {d.w[l], P.wf[l], g.Cout, g.Cin, g.K, g.K, P.ldf[l], (g.Cin % 32 == 0) ? 2 : 0};
+    jobs[nj++] = {d.w[l], P.wf[l], g.Cout, g.Cin, g.K, g.K, P.ldf[l], (g.Cin % 32 == 0) ? 2 : ((l == 0 && d.conv1_order == 2) ? 5 : 0)};
     if (train && l > 0) jobs[nj++] = {d.w[l], P.wd[l], g.Cout, g.Cin, g.K, g.K, P.ldd[l], 3};
   }
   B200_RC(b200ddp_conv2d_weight_prep_multi(jobs, nj, dev, stream));
@@ -211,7 +213,7 @@ int b200ddp_alexnet_forward(void* plan, const float* x, float* out, int train, u
   const float* in = x;
   for (int l = 0; l < 5; ++l) {
     const ConvGeo& g = kConv[l];
-    const int ko = (g.Cin % 32 == 0) ? 1 : 0;
+    const int ko = (g.Cin % 32 == 0) ? 1 : ((l == 0 && d.conv1_order == 2) ? 2 : 0);
     B200_RC(b200ddp_conv2d_fwd(in, P.wf[l], P.ldf[l], d.b[l], P.y[l], ko ? nullptr : d.conv1_ktab, ko, B, g.Cin, g.H, g.H,
                                g.Cout, g.K, g.K, g.stride, g.pad, g.relu_epilogue, dev, stream));
     if (g.pool) {

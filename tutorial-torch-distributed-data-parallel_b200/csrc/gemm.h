@@ -51,6 +51,14 @@ int tf32_gemm_launch(const float* A, long long lda, int a_mn_major, const float*
 int tma_map_2d(CUtensorMap* map, const float* base, long long inner, long long outer, long long ld, int box_inner,
                int box_outer, int swizzle_base32b);
 
+// N-D (2..5) fp32 tiled tensor map without swizzle: gdim[0] is the contiguous dimension, gstr[i] = byte stride of dimension
+// i+1, box = elements per dimension. Out-of-range elements of a box read as zero.
+int tma_map_nd(CUtensorMap* map, const float* base, int rank, const long long* gdim, const long long* gstr_bytes, const int* box);
+
+// First-layer kernel (conv1.cu): k_order 2 of b200ddp_conv2d_fwd.
+int conv1_fwd_launch(const float* x, const float* wmat, long long ldw, const float* bias, float* y, int Nb, int Cin, int H,
+                     int W, int Cout, int KH, int KW, int stride, int pad, int relu, cudaStream_t stream);
+
 // 128-row sub-tiles per CTA that tf32_gemm_launch uses for an M x N x R problem. The kernel supports 2 (two TMEM
 // accumulators sharing one B tile, parity-tested), but on the classifier GEMMs it measured SLOWER than 1
 // (FC1 forward 57 vs 50 us, dX 53 vs 47 us on B200): those kernels are bound by the per-SM TMA fill rate

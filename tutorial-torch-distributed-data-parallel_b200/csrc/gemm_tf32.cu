@@ -203,6 +203,31 @@ int tma_map_2d(CUtensorMap* map, const float* base, long long inner, long long o
   return 0;
 }
 
+int tma_map_nd(CUtensorMap* map, const float* base, int rank, const long long* gdim, const long long* gstr_bytes, const int* box) {
+  int rc0 = get_encode();
+  if (rc0) return rc0;
+  if (rank < 2 || rank > 5) {
+    set_error("tma_map_nd: rank %d", rank);
+    return kInvalidArg;
+  }
+  cuuint64_t gd[5], gs[4];
+  cuuint32_t bx[5], es[5];
+  for (int i = 0; i < rank; ++i) {
+    gd[i] = (cuuint64_t)gdim[i];
+    bx[i] = (cuuint32_t)box[i];
+    es[i] = 1;
+    if (i + 1 < rank) gs[i] = (cuuint64_t)gstr_bytes[i];
+  }
+  CUresult r = g_encode(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, (cuuint32_t)rank, const_cast<float*>(base), gd, gs, bx, es,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_error("cuTensorMapEncodeTiled (rank %d) failed (CUresult %d)", rank, (int)r);
+    return kDriverErrBase + (int)r;
+  }
+  return 0;
+}
+
 namespace {
 
 template <int BN, bool EPI, int RS>
