@@ -211,7 +211,8 @@ int b200ddp_image_transform(const unsigned char* img, const unsigned char* flip,
 int b200ddp_conv2d_fwd(const float* x, const float* wmat, long long ldw, const float* bias, float* y, const int* ktab,
                        int k_order, int Nb, int Cin, int H, int W, int Cout, int KH, int KW, int stride, int pad, int relu,
                        int device, void* stream);
-/* dw [Cout][Cin*KH*KW] = sum over pixels of dy x im2col(x) (written, not accumulated). */
+/* dw [Cout][Cin*KH*KW] = sum over pixels of dy x im2col(x) (written, not accumulated). k_order 2 = the first layer's own
+ * kernel (conv1.cu, same geometry limits as the forward); the workspace query covers it. */
 long long b200ddp_conv2d_wgrad_workspace_bytes(int Nb, int Cin, int H, int W, int Cout, int KH, int KW, int stride,
                                                int pad);
 int b200ddp_conv2d_wgrad(const float* x, const float* dy, float* dw, const int* ktab, int k_order, int Nb, int Cin, int H,

@@ -192,6 +192,10 @@ for (Cin, H, Cout, K, s_, p_, tag) in ((3, 224, 64, 11, 4, 2, "conv1"), (64, 27,
     timeit(f"conv2d_wgrad {tag} (k_order {ko}, incl. split finalize)",
            lambda: chk(L.b200ddp_conv2d_wgrad(xin.data_ptr(), dyc.data_ptr(), dwc.data_ptr(), _lib.ptr(ktab), ko, B, Cin, H, H,
                                               Cout, K, K, s_, p_, wsc.data_ptr(), wsc.numel(), 0, st()), "wgrad"), yb_, fl)
+    if bnn._use_slab(Cin, K, K, s_, Cout, H, p_):
+        timeit(f"conv2d_wgrad {tag} (k_order 2, slab kernel, incl. finalize)",
+               lambda: chk(L.b200ddp_conv2d_wgrad(xin.data_ptr(), dyc.data_ptr(), dwc.data_ptr(), None, 2, B, Cin, H, H,
+                                                  Cout, K, K, s_, p_, wsc.data_ptr(), wsc.numel(), 0, st()), "wgrad"), yb_, fl)
     if s_ == 1:
         kod = bnn._k_order(Cout)
         wt, ldt = bnn.conv_weight_matrix(w, 3 if kod else 1)

@@ -431,7 +431,7 @@ class _Conv2dFn(torch.autograd.Function):
         dw = None
         if ctx.needs_input_grad[1]:
             dw, adopted = _grad_target(ctx.weight_param, tuple(w.shape), x.device)
-            ko = _k_order(Cin)
+            ko = 2 if _use_slab(Cin, KH, KW, stride, Cout, W, pad) else _k_order(Cin)
             ktab = _conv_tables(x.device, Cin, H, W, KH, KW) if ko == 0 else None
             nb = int(L.b200ddp_conv2d_wgrad_workspace_bytes(N, Cin, H, W, Cout, KH, KW, stride, pad))
             wst = st

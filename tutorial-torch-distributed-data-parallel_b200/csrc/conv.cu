@@ -936,14 +936,24 @@ long long b200ddp_conv2d_wgrad_workspace_bytes(int Nb, int Cin, int H, int W, in
                                                int pad) {
   const int OH = (H + 2 * pad - KH) / stride + 1, OW = (W + 2 * pad - KW) / stride + 1;
   const WgradPlan w = plan_wgrad(Nb, Cin, OH, OW, Cout, KH, KW);
-  return w.splits > 1 ? (long long)w.splits * Cout * Cin * KH * KW * 4 : 0;
+  long long need = w.splits > 1 ? (long long)w.splits * Cout * Cin * KH * KW * 4 : 0;
+  if (Cin == 3 && KH == 11 && KW == 11 && stride == 4 && pad == 2 && Cout == 64) {     // also enough for k_order 2 (conv1.cu)
+    const long long slab = conv1_wgrad_workspace_bytes(Nb, H, W, pad);
+    if (slab > need) need = slab;
+  }
+  return need;
 }
 
 int b200ddp_conv2d_wgrad(const float* x, const float* dy, float* dw, const int* ktab, int k_order, int Nb, int Cin, int H,
                          int W, int Cout, int KH, int KW, int stride, int pad, void* ws, long long ws_bytes, int device,
                          void* stream) {
   B200_CHECK_ARG(x && dy && dw, "conv2d_wgrad: null argument");
-  B200_CHECK_ARG(k_order == 0 || k_order == 1, "conv2d_wgrad: k_order must be 0 or 1");
+  if (k_order == 2) {       // the first layer's own kernel (conv1.cu)
+    B200_CHECK_ARG(Nb > 0 && H > 0 && W > 0, "conv2d_wgrad: bad shape");
+    B200_DEVICE(device);
+    return conv1_wgrad_launch(x, dy, dw, Nb, Cin, H, W, Cout, KH, KW, stride, pad, ws, ws_bytes, as_stream(stream));
+  }
+  B200_CHECK_ARG(k_order == 0 || k_order == 1, "conv2d_wgrad: k_order must be 0, 1 or 2 (first layer)");
   B200_CHECK_ARG(k_order == 1 || (ktab && ((uintptr_t)ktab & 7) == 0), "conv2d_wgrad: k_order 0 needs an 8-byte aligned ktab");
   B200_CHECK_ARG(k_order == 0 || (Cin % 32) == 0, "conv2d_wgrad: k_order 1 needs Cin %% 32 == 0 (Cin = %d)", Cin);
   B200_CHECK_ARG(k_order == 1 || (KH <= 15 && KW <= 15), "conv2d_wgrad: k_order 0 supports kernel sizes up to 15 (got %dx%d)", KH, KW);

@@ -309,7 +309,7 @@ int b200ddp_alexnet_backward(void* plan, const float* x, const float* dlogits, f
         if (ready) ready(user, 2);
       }
     } else {
-      B200_RC(b200ddp_conv2d_wgrad(xin, P.dzc[0], dw[0], d.conv1_ktab, 0, B, g.Cin, g.H, g.H, g.Cout, g.K, g.K, g.stride,
+      B200_RC(b200ddp_conv2d_wgrad(xin, P.dzc[0], dw[0], d.conv1_ktab, d.conv1_order == 2 ? 2 : 0, B, g.Cin, g.H, g.H, g.Cout, g.K, g.K, g.stride,
                                    g.pad, P.wg_ws, P.wg_ws_bytes, dev, stream));
       if (ready) ready(user, 3);
     }

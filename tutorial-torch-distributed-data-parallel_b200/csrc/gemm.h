@@ -59,6 +59,10 @@ int tma_map_nd(CUtensorMap* map, const float* base, int rank, const long long* g
 int conv1_fwd_launch(const float* x, const float* wmat, long long ldw, const float* bias, float* y, int Nb, int Cin, int H,
                      int W, int Cout, int KH, int KW, int stride, int pad, int relu, cudaStream_t stream);
 
+long long conv1_wgrad_workspace_bytes(int Nb, int H, int W, int pad);
+int conv1_wgrad_launch(const float* x, const float* dy, float* dw, int Nb, int Cin, int H, int W, int Cout, int KH, int KW,
+                       int stride, int pad, void* ws, long long ws_bytes, cudaStream_t stream);
+
 // 128-row sub-tiles per CTA that tf32_gemm_launch uses for an M x N x R problem. The kernel supports 2 (two TMEM
 // accumulators sharing one B tile, parity-tested), but on the classifier GEMMs it measured SLOWER than 1
 // (FC1 forward 57 vs 50 us, dX 53 vs 47 us on B200): those kernels are bound by the per-SM TMA fill rate
