@@ -258,7 +258,8 @@ conv1_fwd_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
 //     k' = (ci, kh, kw) and walks the pixels: consecutive lanes are consecutive kw, i.e. consecutive words of the slab;
 //   * B = the dY tile [64 channels][112 pixel columns], K-major SWIZZLE_128B in shared memory. dY cannot come through
 //     TMA (its row and plane strides, 220 and 12,100 bytes, are not multiples of 16), so four loader warps read it with
-//     coalesced loads (lane = pixel) and store it swizzled, rounded to TF32;
+//     coalesced asynchronous 4-byte copies (lane = pixel) straight into the swizzled layout (the tensor core truncates
+//     this operand to TF32);
 //   * the four 128 x 64 accumulators stay in TMEM across ALL tiles of a CTA; each CTA writes one partial [408][64] at the
 //     end and conv1_wgrad_finalize_kernel adds the partials in a fixed order (deterministic) into torch's layout.
 constexpr int kWgCols = 112;                       // pixel columns per tile: 2 rows x (55 + 1 zero)
@@ -332,6 +333,7 @@ conv1_wgrad_kernel(const __grid_constant__ CUtensorMap tmX, Conv1WgradParams p) 
     for (int i = 0; i < my_tiles; ++i) {
       const int tb = i & 1;
       mbar_wait(&b_full[tb], ((uint32_t)i >> 1) & 1u);
+      fence_proxy_async_smem();                                        // the tile was written by cp.async (generic proxy)
       const uint32_t b_saddr = smem_u32(s_b + tb * kWgBBytes);
       for (int mt = 0; mt < kWgMTiles; ++mt) {
         const int st = mt & 1;
@@ -426,33 +428,25 @@ conv1_wgrad_kernel(const __grid_constant__ CUtensorMap tmX, Conv1WgradParams p) 
       mbar_wait(&b_empty[tb], (((uint32_t)i >> 1) & 1u) ^ 1u);
       const uint32_t bb = smem_u32(s_b + tb * kWgBBytes);
       const float* dyn = p.dy + (long long)n * kC1BN * ohw;
-#pragma unroll 1
-      for (int cc = 0; cc < 16; cc += 4) {
-        float v[4][4];
+      // asynchronous 4-byte copies global -> shared (dY rows are only 4-byte aligned), zero-filled where the column is
+      // padding or beyond the image; the barrier is signalled by the copy unit when this thread's copies have landed,
+      // so the loader goes straight on to the next tile and ~8 KB per warp are in flight without holding registers
+#pragma unroll 4
+      for (int u = 0; u < 16; ++u) {
+        const int co = lw * 16 + u;
 #pragma unroll
-        for (int u = 0; u < 4; ++u) {
-          const int co = lw * 16 + cc + u;
-#pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            const int c = j * 32 + lane;                               // pixel column of the tile
-            const int row = c >= kWgRowCols ? 1 : 0, ow = c - row * kWgRowCols;
-            const bool ok = c < kWgCols && ow < p.OW && oh0 + row < p.OH;
-            v[u][j] = ok ? __ldg(dyn + (long long)co * ohw + (long long)(oh0 + row) * p.OW + ow) : 0.f;
-          }
-        }
-#pragma unroll
-        for (int u = 0; u < 4; ++u) {
-          const int co = lw * 16 + cc + u;
-#pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            const uint32_t a = bb + (uint32_t)j * (kC1BN * 128) + (uint32_t)co * 128u +
-                               ((((uint32_t)lane >> 2) ^ ((uint32_t)co & 7u)) << 4) + ((uint32_t)lane & 3u) * 4u;
-            asm volatile("st.shared.b32 [%0], %1;" ::"r"(a), "r"(rtf32(v[u][j])) : "memory");
-          }
+        for (int j = 0; j < 4; ++j) {
+          const int c = j * 32 + lane;                                 // pixel column of the tile
+          const int row = c >= kWgRowCols ? 1 : 0, ow = c - row * kWgRowCols;
+          const bool ok = c < kWgCols && ow < p.OW && oh0 + row < p.OH;
+          const float* src = ok ? dyn + (long long)co * ohw + (long long)(oh0 + row) * p.OW + ow : dyn;
+          const uint32_t a = bb + (uint32_t)j * (kC1BN * 128) + (uint32_t)co * 128u +
+                             ((((uint32_t)lane >> 2) ^ ((uint32_t)co & 7u)) << 4) + ((uint32_t)lane & 3u) * 4u;
+          asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(a), "l"(src), "r"(ok ? 4 : 0) : "memory");
         }
       }
-      fence_proxy_async_smem();
-      mbar_arrive(&b_full[tb]);
+      asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(smem_u32(&b_full[tb])) : "memory");
+
     }
   }
   tc_fence_before();
