@@ -547,6 +547,10 @@ int conv1_wgrad_launch(const float* x, const float* dy, float* dw, int Nb, int C
   B200_CHECK_ARG(p.OH > 0 && p.OW > 0 && p.OW < kWgRowCols, "conv2d_wgrad k_order 2: output rows of at most %d pixels (got %d)",
                  kWgRowCols - 1, p.OW);
   p.in_cols = (kC1Stride * (p.OW - 1) + kC1Shift + kC1KW + 3) / 4 * 4;
+  // A gather warp reads, per pixel, 11 + 11 + 8 consecutive words of three consecutive slab rows (lanes = 12-padded kernel
+  // rows): with a row pitch of 12 (mod 32) words the three runs fall on disjoint banks; any other pitch costs a second
+  // wavefront per load (ncu: the shared-memory pipe is the busiest unit of this kernel)
+  while ((p.in_cols & 31) != 12) p.in_cols += 4;
   B200_CHECK_ARG(p.in_cols <= 256, "conv2d_wgrad k_order 2: input rows too wide");
   p.tiles_per_image = (p.OH + kC1TileRows - 1) / kC1TileRows;
   p.tiles = p.tiles_per_image * Nb;
