@@ -918,6 +918,8 @@ def run_b200(args) -> None:
     #      a kernel that shares the SMs with another stream's kernel measures the interference, not the kernel) ----------
     prev_side = os.environ.get("B200DDP_WGRAD_SIDE_STREAM")
     os.environ["B200DDP_WGRAD_SIDE_STREAM"] = "0"
+    prev_engine = os.environ.get("B200DDP_ENGINE")
+    os.environ["B200DDP_ENGINE"] = "0"         # per-layer module path: the same kernels, one timed C-ABI call each
     was_overlap, opt.overlap_backward = opt.overlap_backward, False
     _lib.enable_timing()
     n_prof = min(args.steps, 10)
@@ -925,6 +927,10 @@ def run_b200(args) -> None:
         job.step_resident()
     calls = _lib.disable_timing()
     opt.overlap_backward = was_overlap
+    if prev_engine is None:
+        del os.environ["B200DDP_ENGINE"]
+    else:
+        os.environ["B200DDP_ENGINE"] = prev_engine
     if prev_side is None:
         del os.environ["B200DDP_WGRAD_SIDE_STREAM"]
     else:

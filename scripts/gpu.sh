@@ -48,8 +48,12 @@ case "$what" in
     # sweep N VAR v1 v2 ... : bench.py at N ranks (30 steps, timed regions only) for each value of environment variable VAR
     n=$1; var=$2; shift 2
     for v in "$@"; do
-      env $var=$v timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port 29512 \
-        bench.py --gpus $n --steps 30 --warmup 5 --no-extras > gpurun_out/sweep_${var}_$v.log 2>gpurun_out/sweep_${var}_$v.err
+      if [ "$n" = "1" ]; then
+        env $var=$v timeout 600 python bench.py --steps 100 --warmup 5 --no-extras > gpurun_out/sweep_${var}_$v.log 2>gpurun_out/sweep_${var}_$v.err
+      else
+        env $var=$v timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port 29512 \
+          bench.py --gpus $n --steps 30 --warmup 5 --no-extras > gpurun_out/sweep_${var}_$v.log 2>gpurun_out/sweep_${var}_$v.err
+      fi
       python - "$var=$v" gpurun_out/sweep_${var}_$v.log <<'PY'
 import json, sys
 try:

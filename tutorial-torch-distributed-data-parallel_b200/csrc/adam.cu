@@ -22,6 +22,27 @@ struct AdamScalars {
   float weight_decay;
 };
 
+// The optimizer streams 28 bytes per parameter exactly once while (inside backward) the convolution kernels next to it
+// live off activations that sit in the 126 MB L2: every access carries an evict-first L2 policy so that the stream does
+// not push those activations out.
+__device__ __forceinline__ uint64_t evict_first_policy() {
+  uint64_t pol;
+  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+  return pol;
+}
+__device__ __forceinline__ float4 ld_ef(const float4* p, uint64_t pol) {
+  float4 r;
+  asm volatile("ld.global.L1::no_allocate.L2::cache_hint.v4.f32 {%0,%1,%2,%3}, [%4], %5;"
+               : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w)
+               : "l"(p), "l"(pol));
+  return r;
+}
+__device__ __forceinline__ void st_ef(float4* p, const float4& v, uint64_t pol) {
+  asm volatile("st.global.L1::no_allocate.L2::cache_hint.v4.f32 [%0], {%1,%2,%3,%4}, %5;" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z),
+               "f"(v.w), "l"(pol)
+               : "memory");
+}
+
 __device__ __forceinline__ void adam_one(float& p, float g, float& m, float& v, const AdamScalars& s,
                                          float gscale) {
   g *= gscale;
@@ -32,11 +53,16 @@ __device__ __forceinline__ void adam_one(float& p, float g, float& m, float& v, 
   p = fmaf(s.neg_step_size, m / denom, p);
 }
 
-__global__ void __launch_bounds__(256) adam_flat_kernel(float* __restrict__ p, const float* __restrict__ g,
+// 128-thread CTAs on purpose: when the optimizer runs per bucket INSIDE backward (reducer._fused_adam), its CTAs have to
+// squeeze in beside a convolution CTA that holds 57,344 of the SM's 65,536 registers; 128 threads x 40 registers fit
+// the remaining 8,192, 256 threads do not (they would only run in the gaps between convolution kernels).
+constexpr int kAdamThreads = 128;
+__global__ void __launch_bounds__(kAdamThreads) adam_flat_kernel(float* __restrict__ p, const float* __restrict__ g,
                                                         float* __restrict__ m, float* __restrict__ v,
                                                         long long n, AdamScalars s,
                                                         const float* __restrict__ gscale_dev) {
   const float gscale = gscale_dev ? __ldg(gscale_dev) : 1.0f;
+  const uint64_t pol = evict_first_policy();
   const long long n4 = n >> 2;
   const long long stride = (long long)gridDim.x * blockDim.x;
   float4* p4 = reinterpret_cast<float4*>(p);
@@ -44,17 +70,17 @@ __global__ void __launch_bounds__(256) adam_flat_kernel(float* __restrict__ p, c
   float4* m4 = reinterpret_cast<float4*>(m);
   float4* v4 = reinterpret_cast<float4*>(v);
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += stride) {
-    float4 pp = ld_f4(p4 + i);
-    const float4 gg = ld_stream(g4 + i);
-    float4 mm = ld_f4(m4 + i);
-    float4 vv = ld_f4(v4 + i);
+    float4 pp = ld_ef(p4 + i, pol);
+    const float4 gg = ld_ef(g4 + i, pol);
+    float4 mm = ld_ef(m4 + i, pol);
+    float4 vv = ld_ef(v4 + i, pol);
     adam_one(pp.x, gg.x, mm.x, vv.x, s, gscale);
     adam_one(pp.y, gg.y, mm.y, vv.y, s, gscale);
     adam_one(pp.z, gg.z, mm.z, vv.z, s, gscale);
     adam_one(pp.w, gg.w, mm.w, vv.w, s, gscale);
-    p4[i] = pp;          // params are re-read by the next forward: keep them cacheable
-    st_stream(m4 + i, mm);
-    st_stream(v4 + i, vv);
+    st_ef(p4 + i, pp, pol);
+    st_ef(m4 + i, mm, pol);
+    st_ef(v4 + i, vv, pol);
   }
   // scalar tail (n % 4 elements)
   const long long tail0 = n4 << 2;
@@ -92,11 +118,11 @@ extern "C" int b200ddp_adam_step_flat(float* p, const float* g, float* m, float*
   s.eps = (float)eps;
   s.weight_decay = (float)weight_decay;
   const long long n4 = n >> 2;
-  long long want = (n4 + 255) / 256;
+  long long want = (n4 + kAdamThreads - 1) / kAdamThreads;
   if (want < 1) want = 1;
-  const long long cap = (long long)num_sms() * 8;
+  const long long cap = (long long)num_sms() * 16;
   const int grid = (int)(want < cap ? want : cap);
-  adam_flat_kernel<<<grid, 256, 0, as_stream(stream)>>>(p, g, m, v, n, s, grad_scale_dev);
+  adam_flat_kernel<<<grid, kAdamThreads, 0, as_stream(stream)>>>(p, g, m, v, n, s, grad_scale_dev);
   B200_LAUNCH_OK();
   return 0;
 }

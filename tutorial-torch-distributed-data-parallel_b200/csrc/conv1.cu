@@ -454,18 +454,22 @@ conv1_wgrad_kernel(const __grid_constant__ CUtensorMap tmX, Conv1WgradParams p) 
   if (warp == 1) tmem_dealloc(tmem_base, 512);
 }
 
-// dW[co][ci][kh][kw] = sum over CTAs (in CTA order) of partial[cta][ci*136 + kh*12 + kw][co]
+// dW[co][ci][kh][kw] = sum over CTAs of partial[cta][ci*136 + kh*12 + kw][co], in a fixed order: a warp owns 8
+// consecutive output channels of one (ci, kh, kw); its four lane groups add every fourth partial, then the four sums are
+// combined by two shuffle steps (deterministic).
 __global__ void __launch_bounds__(256) conv1_wgrad_finalize_kernel(const float* __restrict__ partial, int nparts,
                                                                    float* __restrict__ dw) {
-  const int total = kC1Cin * kC1KH * kC1KW * kC1BN;
-  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
-    const int co = i % kC1BN, kr = i / kC1BN;                           // kr = (ci, kh, kw) in torch order
-    const int ci = kr / (kC1KH * kC1KW), rem = kr - ci * (kC1KH * kC1KW), kh = rem / kC1KW, kw = rem - kh * kC1KW;
-    const float* src = partial + (size_t)(ci * kC1StageCols + kh * kC1RowCols + kw) * kC1BN + co;
-    float acc = 0.f;
-    for (int z = 0; z < nparts; ++z) acc += __ldg(src + (size_t)z * kC1K * kC1BN);
-    dw[(size_t)co * (kC1Cin * kC1KH * kC1KW) + kr] = acc;
-  }
+  const int total8 = kC1Cin * kC1KH * kC1KW * (kC1BN / 8);
+  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (warp >= total8) return;
+  const int kr = warp / (kC1BN / 8), co = (warp - kr * (kC1BN / 8)) * 8 + (lane & 7), zp = lane >> 3;
+  const int ci = kr / (kC1KH * kC1KW), rem = kr - ci * (kC1KH * kC1KW), kh = rem / kC1KW, kw = rem - kh * kC1KW;
+  const float* src = partial + (size_t)(ci * kC1StageCols + kh * kC1RowCols + kw) * kC1BN + co;
+  float acc = 0.f;
+  for (int z = zp; z < nparts; z += 4) acc += __ldg(src + (size_t)z * kC1K * kC1BN);
+  acc += __shfl_xor_sync(0xffffffffu, acc, 8);
+  acc += __shfl_xor_sync(0xffffffffu, acc, 16);
+  if (zp == 0) dw[(size_t)co * (kC1Cin * kC1KH * kC1KW) + kr] = acc;
 }
 
 }  // namespace
@@ -582,7 +586,7 @@ int conv1_wgrad_launch(const float* x, const float* dy, float* dw, int Nb, int C
   }
   count_launch();
   const int total = kC1Cin * kC1KH * kC1KW * kC1BN;
-  conv1_wgrad_finalize_kernel<<<(total + 255) / 256, 256, 0, stream>>>(p.partial, grid, dw);
+  conv1_wgrad_finalize_kernel<<<(total * 4 + 255) / 256, 256, 0, stream>>>(p.partial, grid, dw);
   e = cudaGetLastError();
   if (e != cudaSuccess) {
     set_error("conv1_wgrad_finalize_kernel launch -> %s", cudaGetErrorString(e));
