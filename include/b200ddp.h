@@ -106,6 +106,12 @@ int b200ddp_comm_set_algo(void* handle, int algo, int ctas);
 /* CTA shape of that kernel: 0 = 256 threads x 32 registers (fits beside a running convolution CTA), 1 = 1024 threads
  * (owns its SM; leave `ctas` SMs out of the compute grids with b200ddp_set_sm_budget). */
 int b200ddp_comm_set_cta_shape(void* handle, int big);
+/* B1: the two tiny collectives of SyncBatchNorm (torch _functions.py:50-75 all_gather of [mean, invstd, count], :160-170
+ * all_reduce of [sum_dy, sum_dy_xmu]) as ONE single-CTA kernel over the communicator's peer / multicast mappings: every
+ * rank deposits its n <= 2048 floats in every rank's scratch, one flag round, then sum_mode 0: out [nranks][n] (all-gather),
+ * 1: out [n] = scale * sum in rank order (bit-identical everywhere). Caller's stream. Returns 2 (not initialised) when the
+ * peer path is unavailable: use comm_allgather / comm_allreduce then. COLLECTIVE on first use (set-up). */
+int b200ddp_comm_small_collective(void* handle, const float* send, float* out, int n, int sum_mode, float scale, void* stream);
 /* Device time of each bucket collective of the last joined backward pass (for the NVLink roofline: busBW =
  * 4 n * 2 (ws-1)/ws / t). set_timing(1) first; synchronise before reading. Returns the number of entries. */
 int b200ddp_comm_set_timing(void* handle, int on);

@@ -399,3 +399,35 @@ def case_fused_adam_in_backward_is_bitwise(rank, world, out_dir, dev):
     assert torch.equal(outs[0], outs[1])
     ps = _gather_params(model, world)
     assert all(torch.equal(ps[0], t) for t in ps)
+
+
+def case_small_collectives(rank, world, out_dir, dev):
+    """B1: the SyncBatchNorm-sized all-gather / rank-ordered sum kernel over peer memory, 200 calls in a row with
+    changing sizes (flag epochs, scratch parity), against torch.distributed."""
+    from b200ddp.comm import get_comm
+    comm = get_comm(dev, None)
+    g = torch.Generator(device=dev).manual_seed(7 + rank)
+    used = 0
+    for it in range(200):
+        n = [1, 129, 513, 2048, 769][it % 5]
+        send = torch.randn(n, device=dev, generator=g)
+        if it % 2 == 0:
+            out = torch.empty(world * n, device=dev)
+            ok = comm.small_collective(send, out, sum_mode=False)
+            ref = [torch.empty_like(send) for _ in range(world)]
+            dist.all_gather(ref, send)
+            if ok:
+                assert torch.equal(out, torch.cat(ref)), it
+        else:
+            out = torch.empty(n, device=dev)
+            ok = comm.small_collective(send, out, sum_mode=True, scale=0.5)
+            ref = send.clone()
+            dist.all_reduce(ref)
+            if ok:
+                assert torch.allclose(out, ref * 0.5, rtol=1e-6, atol=1e-6), it
+                box = [torch.empty_like(out) for _ in range(world)]
+                dist.all_gather(box, out)
+                assert all(torch.equal(box[0], t) for t in box)          # rank-ordered sum: same bits everywhere
+        used += int(ok)
+    with open(os.path.join(out_dir, f"small_rank{rank}.txt"), "w") as fh:
+        fh.write(str(used))

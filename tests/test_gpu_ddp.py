@@ -33,3 +33,8 @@ def test_syncbn_two_ranks_matches_global_batch(tmp_path):
 def test_own_allreduce_kernel_known_values(tmp_path):
     _spawn(_workers.run, "own_allreduce_known_values", tmp_path)
     print("arena mode / peer path:", open(os.path.join(str(tmp_path), "arena_mode_rank0.txt")).read())
+
+
+def test_small_collectives_over_peer_memory(tmp_path):
+    _spawn(_workers.run, "small_collectives", tmp_path)
+    print("small collectives served by the peer kernel:", open(os.path.join(str(tmp_path), "small_rank0.txt")).read(), "of 200")

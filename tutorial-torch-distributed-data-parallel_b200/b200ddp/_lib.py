@@ -69,6 +69,7 @@ _PROTOS = {
     "b200ddp_bucket_wait_last": (c_int, [_P, _P]),
     "b200ddp_comm_arena_alloc": (c_int, [_P, c_longlong, POINTER(c_void_p), POINTER(c_int)]),
     "b200ddp_comm_set_algo": (c_int, [_P, c_int, c_int]),
+    "b200ddp_comm_small_collective": (c_int, [_P, _P, _P, c_int, c_int, c_float, _P]),
     "b200ddp_comm_set_cta_shape": (c_int, [_P, c_int]),
     "b200ddp_comm_set_timing": (c_int, [_P, c_int]),
     "b200ddp_comm_bucket_times": (c_int, [_P, POINTER(c_float), POINTER(c_longlong), c_int]),

@@ -27,6 +27,7 @@ class NativeComm:
         self.world = world
         self.device = device
         self.arena_mode = 0
+        self._small_ok = None
         self.algo = "ring"
         self._arenas = []
 
@@ -51,6 +52,20 @@ class NativeComm:
         L = _lib.load()
         _lib.check(L.b200ddp_bucket_reduce_launch(self.handle, ptr, n, premul, _lib.cur_stream(device)),
                    "bucket_reduce_launch")
+
+    def small_collective(self, send: torch.Tensor, out: torch.Tensor, sum_mode: bool, scale: float = 1.0) -> bool:
+        """SyncBatchNorm-sized all-gather (out [world, n]) or rank-ordered sum (out [n]) as one kernel over peer memory
+        (b200ddp_comm_small_collective). False = peer path unavailable, nothing was launched: use NCCL."""
+        if self._small_ok is False or send.numel() > 2048 or os.environ.get("B200DDP_SMALL_COLLECTIVES", "own") != "own":
+            return False
+        rc = _lib.load().b200ddp_comm_small_collective(self.handle, send.data_ptr(), out.data_ptr(), send.numel(),
+                                                       int(bool(sum_mode)), float(scale), _lib.cur_stream(send.device))
+        if rc == 2:                       # kNotInitialised: no symmetric memory on this system
+            self._small_ok = False
+            return False
+        _lib.check(rc, "comm_small_collective")
+        self._small_ok = True
+        return True
 
     def bucket_wait_last(self, stream: int) -> None:
         """`stream` (a raw cudaStream_t) waits for the bucket collective launched last."""

@@ -761,7 +761,8 @@ class _SyncBatchNormFn(torch.autograd.Function):
         stats[2 * C].fill_(float(B * HW))
         if world > 1:
             gathered = torch.empty(world * (2 * C + 1), dtype=torch.float32, device=x.device)
-            comm.allgather(stats, gathered)
+            if not comm.small_collective(stats, gathered, sum_mode=False):      # one kernel over peer memory, else NCCL
+                comm.allgather(stats, gathered)
         else:
             gathered = stats
         mean = torch.empty(C, dtype=torch.float32, device=x.device)
@@ -796,7 +797,11 @@ class _SyncBatchNormFn(torch.autograd.Function):
                    "bn_bwd_reduce")
         total = ctx.count_local
         if ctx.world > 1:
-            ctx.comm.allreduce_(sums, 1.0)
+            summed = torch.empty_like(sums)
+            if ctx.comm.small_collective(sums, summed, sum_mode=True):
+                sums = summed
+            else:
+                ctx.comm.allreduce_(sums, 1.0)
             total = ctx.count_local * ctx.world   # equal local batch sizes (DistributedSampler pads)
         dx = None
         if ctx.needs_input_grad[0]:

@@ -128,6 +128,8 @@ struct Comm {
   // peer-memory path (our own all-reduce kernel, peer_allreduce.cu)
   std::vector<SymBuf> bufs;
   SymBuf flags;
+  SymBuf small;              // scratch of the small collectives (SyncBatchNorm statistics)
+  unsigned int small_epoch = 0;
   bool peer_tried = false, peer_ok = false;
   ncclDevComm_t devcomm;
   bool have_devcomm = false;
@@ -186,6 +188,19 @@ static int peer_setup(Comm* c) {
   c->have_devcomm = true;
   if (c->devcomm.lsaSize != c->nranks || c->devcomm.lsaRank != c->rank) return 0;   // ranks outside one NVLink domain
   int rc = fill_map(c, c->flags);
+  if (rc) return rc;
+  // scratch of the small collectives: [2 parities][ranks][kSmallMaxFloats]
+  const size_t sbytes = round_up(kSmallScratchBytes, 2u << 20);
+  B200_NCCL(g_nccl.MemAlloc(&c->small.ptr, sbytes));
+  c->small.bytes = sbytes;
+  B200_CUDA(cudaMemset(c->small.ptr, 0, sbytes));
+  B200_CUDA(cudaDeviceSynchronize());
+  r = g_nccl.CommWindowRegister(c->comm, c->small.ptr, sbytes, &c->small.win, NCCL_WIN_COLL_SYMMETRIC);
+  if (r != ncclSuccess || !c->small.win) {
+    c->small.win = nullptr;
+    return 0;
+  }
+  rc = fill_map(c, c->small);
   if (rc) return rc;
   // nobody may write a flag before everybody has zeroed theirs: one tiny collective as the rendezvous
   float* tmp = nullptr;
@@ -264,6 +279,7 @@ int b200ddp_comm_destroy(void* h) {
   if (c->have_avg_op) g_nccl.RedOpDestroy(c->avg_op, c->comm);
   if (c->have_devcomm && g_nccl.DevCommDestroy) g_nccl.DevCommDestroy(c->comm, &c->devcomm);
   c->bufs.push_back(c->flags);
+  c->bufs.push_back(c->small);
   for (SymBuf& b : c->bufs) {
     if (b.win && g_nccl.CommWindowDeregister) g_nccl.CommWindowDeregister(c->comm, b.win);
     if (b.reg && g_nccl.CommDeregister) g_nccl.CommDeregister(c->comm, b.reg);
@@ -395,6 +411,31 @@ int b200ddp_bucket_reduce_join(void* h, void* compute_stream) {
   c->last_count = c->timing ? c->inflight : 0;
   c->inflight = 0;
   return 0;
+}
+
+// Small latency-bound collective over peer memory (B1: SyncBatchNorm statistics): sum_mode 0 = all-gather, out
+// [nranks][n]; 1 = sum over ranks in rank order times `scale`, out [n] (bit-identical on every rank). n <= 2048 floats,
+// on the CALLER's stream. Returns kNotInitialised when the peer path does not exist (the caller then uses NCCL).
+int b200ddp_comm_small_collective(void* h, const float* send, float* out, int n, int sum_mode, float scale, void* stream) {
+  B200_CHECK_ARG(h && send && out, "comm_small_collective: null argument");
+  Comm* c = reinterpret_cast<Comm*>(h);
+  if (!c->peer_tried) {
+    B200_DEVICE(c->device);
+    int rc = peer_setup(c);
+    if (rc) return rc;
+  }
+  if (!c->peer_ok || !c->small.win || n > kSmallMaxFloats) {
+    set_error("comm_small_collective: peer path unavailable or message too large (%d floats)", n);
+    return kNotInitialised;
+  }
+  B200_DEVICE(c->device);
+  PeerArgs a;
+  a.data = c->small.map;
+  a.flags = c->flags.map;
+  a.rank = c->rank;
+  a.nranks = c->nranks;
+  a.epoch = ++c->small_epoch;
+  return peer_small_collective_launch(a, send, out, n, sum_mode, scale, as_stream(stream));
 }
 
 // ---- arena_register: the gradient arena as an NCCL-registered, peer-mapped buffer -------------------

@@ -29,4 +29,13 @@ struct PeerArgs {
 int peer_allreduce_launch(const PeerArgs& a, long long off_bytes, long long n, float scale, int ctas, int big_ctas,
                           cudaStream_t stream);
 
+// Small, latency-bound collectives (SyncBatchNorm statistics, B1) over the same mappings: every rank deposits its
+// `n` floats (n <= kSmallMaxFloats) in slot [parity][rank] of every rank's scratch buffer, one flag round later every
+// rank holds all contributions. out: [nranks][n] (sum_mode 0, all-gather) or [n] (sum_mode 1: sum in rank order, times
+// `scale` - identical bits on every rank). One CTA; a.data = the scratch buffer's map, a.epoch = this call's epoch.
+constexpr int kSmallMaxFloats = 2048;
+constexpr size_t kSmallScratchBytes = 2ull * kPeerMaxRanks * kSmallMaxFloats * sizeof(float);
+int peer_small_collective_launch(const PeerArgs& a, const float* send, float* out, int n, int sum_mode, float scale,
+                                 cudaStream_t stream);
+
 }  // namespace b200

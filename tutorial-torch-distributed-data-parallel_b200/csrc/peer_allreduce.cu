@@ -60,6 +60,11 @@ __device__ __forceinline__ float4 ld_sys_f4(const float4* p) {
   asm volatile("ld.relaxed.sys.global.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
   return v;
 }
+__device__ __forceinline__ float ld_sys_f4_scalar(const float* p) {
+  float v;
+  asm volatile("ld.relaxed.sys.global.f32 %0, [%1];" : "=f"(v) : "l"(p) : "memory");
+  return v;
+}
 __device__ __forceinline__ float4 mm_ld_reduce(const float* mc) {
   float4 v;
   asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
@@ -147,13 +152,72 @@ peer_allreduce_kernel(PeerArgs a, long long off_bytes, long long n4, float scale
 
 }  // namespace
 
+// One CTA. Flags: the last CTA slot of the flag buffer (the bucket all-reduce never uses kPeerMaxCtas CTAs).
+__global__ void __launch_bounds__(256) peer_small_collective_kernel(PeerArgs a, const float* __restrict__ send,
+                                                                    float* __restrict__ out, int n, int sum_mode, float scale) {
+  const unsigned parity = a.epoch & 1u;
+  const size_t slot = ((size_t)parity * kPeerMaxRanks + (size_t)a.rank) * kSmallMaxFloats;
+  if (a.data.mc) {
+    float* dst = reinterpret_cast<float*>(a.data.mc) + slot;                    // one store reaches every rank
+    for (int i = threadIdx.x; i < n; i += blockDim.x)
+      asm volatile("multimem.st.relaxed.sys.global.f32 [%0], %1;" ::"l"(dst + i), "f"(send[i]) : "memory");
+  } else {
+    for (int p = 0; p < a.nranks; ++p) {
+      float* dst = reinterpret_cast<float*>(a.data.peer[p]) + slot;
+      for (int i = threadIdx.x; i < n; i += blockDim.x) dst[i] = send[i];
+    }
+  }
+  __threadfence_system();
+  // flag round on slot kPeerMaxCtas - 1 (peer_barrier indexes by blockIdx.x == 0, so address it by hand)
+  __syncthreads();
+  const int t = threadIdx.x;
+  if (t < a.nranks && t != a.rank) {
+    const size_t fs = (size_t)(kPeerMaxCtas - 1) * kPeerMaxRanks;
+    st_release_sys(reinterpret_cast<unsigned int*>(a.flags.peer[t]) + fs + a.rank, a.epoch);
+    const unsigned int* mine = reinterpret_cast<const unsigned int*>(a.flags.peer[a.rank]) + fs + t;
+    unsigned long long t0 = 0;
+    unsigned int spins = 0;
+    while ((int)(ld_acquire_sys(mine) - a.epoch) < 0) {
+      if ((++spins & 0xfffu) == 0) {
+        const unsigned long long now = gtimer();
+        if (t0 == 0) t0 = now;
+        else if (now - t0 > kWaitNs) {
+          printf("b200ddp: small collective timed out (rank %d waits for rank %d, epoch %u)\n", a.rank, t, a.epoch);
+          __trap();
+        }
+      }
+    }
+  }
+  __syncthreads();
+  const float* mine_base = reinterpret_cast<const float*>(a.data.peer[a.rank]) + (size_t)parity * kPeerMaxRanks * kSmallMaxFloats;
+  if (sum_mode) {
+    for (int i = threadIdx.x; i < n; i += blockDim.x) {
+      float acc = 0.f;
+      for (int r = 0; r < a.nranks; ++r) acc += ld_sys_f4_scalar(mine_base + (size_t)r * kSmallMaxFloats + i);
+      out[i] = acc * scale;
+    }
+  } else {
+    for (int r = 0; r < a.nranks; ++r)
+      for (int i = threadIdx.x; i < n; i += blockDim.x) out[(size_t)r * n + i] = ld_sys_f4_scalar(mine_base + (size_t)r * kSmallMaxFloats + i);
+  }
+}
+
+int peer_small_collective_launch(const PeerArgs& a, const float* send, float* out, int n, int sum_mode, float scale,
+                                 cudaStream_t stream) {
+  B200_CHECK_ARG(send && out && n > 0 && n <= kSmallMaxFloats, "small collective: 1..%d floats (got %d)", kSmallMaxFloats, n);
+  B200_CHECK_ARG(a.nranks >= 2 && a.nranks <= kPeerMaxRanks, "small collective: 2..%d ranks", kPeerMaxRanks);
+  peer_small_collective_kernel<<<1, 256, 0, stream>>>(a, send, out, n, sum_mode, scale);
+  B200_LAUNCH_OK();
+  return 0;
+}
+
 int peer_allreduce_launch(const PeerArgs& a, long long off_bytes, long long n, float scale, int ctas, int big_ctas,
                           cudaStream_t stream) {
   B200_CHECK_ARG(n >= 0 && (n & 3) == 0 && (off_bytes & 15) == 0, "peer_allreduce: range must be 16-byte aligned (n = %lld)", n);
   B200_CHECK_ARG(a.nranks >= 2 && a.nranks <= kPeerMaxRanks, "peer_allreduce: 2..%d ranks", kPeerMaxRanks);
   if (n == 0) return 0;
   if (ctas < 1) ctas = 1;
-  if (ctas > kPeerMaxCtas) ctas = kPeerMaxCtas;
+  if (ctas > kPeerMaxCtas - 1) ctas = kPeerMaxCtas - 1;       // the last flag slot belongs to the small collectives
   const long long n4 = n >> 2;
   if (big_ctas) {
     if (a.data.mc) peer_allreduce_kernel<true, kArThreadsBig, kUnrollBig><<<ctas, kArThreadsBig, 0, stream>>>(a, off_bytes, n4, scale);
