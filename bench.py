@@ -49,6 +49,7 @@ def parse():
     ap.add_argument("--hidden", type=int, default=4096)
     ap.add_argument("--batch", type=int, default=BATCH)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--bn", action="store_true", help="AlexNet-BN + convert_sync_batchnorm as the main job (configs[3])")
     ap.add_argument("--no-extras", action="store_true",
                     help="timed regions only: no stock-torch arm, no extra configs, no parity block, no CPU baseline")
     return ap.parse_args()
@@ -843,7 +844,7 @@ def run_b200(args) -> None:
             dist.barrier()
             torch.cuda.synchronize(dev)
 
-    job = Job(args, dev, world, rank, local)
+    job = Job(args, dev, world, rank, local, bn=args.bn)
     ddp, opt = job.ddp, job.opt
     job.prepare_indices(2 * (args.steps + args.warmup) + 200)
     # Reserve the activation pool up front: one block that the caching allocator then carves up, so that no cudaMalloc

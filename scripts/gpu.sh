@@ -52,7 +52,7 @@ case "$what" in
         env $var=$v timeout 600 python bench.py --steps 100 --warmup 5 --no-extras > gpurun_out/sweep_${var}_$v.log 2>gpurun_out/sweep_${var}_$v.err
       else
         env $var=$v timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port 29512 \
-          bench.py --gpus $n --steps 30 --warmup 5 --no-extras > gpurun_out/sweep_${var}_$v.log 2>gpurun_out/sweep_${var}_$v.err
+          bench.py --gpus $n --steps 30 --warmup 5 --no-extras $BENCH_ARGS > gpurun_out/sweep_${var}_$v.log 2>gpurun_out/sweep_${var}_$v.err
       fi
       python - "$var=$v" gpurun_out/sweep_${var}_$v.log <<'PY'
 import json, sys

@@ -405,6 +405,7 @@ def case_small_collectives(rank, world, out_dir, dev):
     """B1: the SyncBatchNorm-sized all-gather / rank-ordered sum kernel over peer memory, 200 calls in a row with
     changing sizes (flag epochs, scratch parity), against torch.distributed."""
     from b200ddp.comm import get_comm
+    os.environ["B200DDP_SMALL_COLLECTIVES"] = "own"          # the peer kernel at every world size (default: auto)
     comm = get_comm(dev, None)
     g = torch.Generator(device=dev).manual_seed(7 + rank)
     used = 0

@@ -158,9 +158,16 @@ __global__ void __launch_bounds__(256) peer_small_collective_kernel(PeerArgs a, 
   const unsigned parity = a.epoch & 1u;
   const size_t slot = ((size_t)parity * kPeerMaxRanks + (size_t)a.rank) * kSmallMaxFloats;
   if (a.data.mc) {
-    float* dst = reinterpret_cast<float*>(a.data.mc) + slot;                    // one store reaches every rank
-    for (int i = threadIdx.x; i < n; i += blockDim.x)
-      asm volatile("multimem.st.relaxed.sys.global.f32 [%0], %1;" ::"l"(dst + i), "f"(send[i]) : "memory");
+    // one store reaches every rank; 16 bytes per packet (the slot is 16-byte aligned and padded, the tail is zero-filled)
+    float* dst = reinterpret_cast<float*>(a.data.mc) + slot;
+    for (int i = threadIdx.x * 4; i < n; i += blockDim.x * 4) {
+      float4 v;
+      v.x = send[i];
+      v.y = i + 1 < n ? send[i + 1] : 0.f;
+      v.z = i + 2 < n ? send[i + 2] : 0.f;
+      v.w = i + 3 < n ? send[i + 3] : 0.f;
+      mm_st(dst + i, v);
+    }
   } else {
     for (int p = 0; p < a.nranks; ++p) {
       float* dst = reinterpret_cast<float*>(a.data.peer[p]) + slot;
