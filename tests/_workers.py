@@ -432,3 +432,14 @@ def case_small_collectives(rank, world, out_dir, dev):
         used += int(ok)
     with open(os.path.join(out_dir, f"small_rank{rank}.txt"), "w") as fh:
         fh.write(str(used))
+
+
+def case_metrics_one_collective(rank, world, out_dir, dev):
+    """f1: all_reduce_metrics = the reference's five scalar all-reduces (torch.py:198-204) as one collective, in place."""
+    import b200ddp
+    a = torch.tensor([1.5 + rank], device=dev)
+    b = torch.tensor([10.0 * (rank + 1)], device=dev)
+    c = torch.tensor([3.0], device=dev)
+    out = b200ddp.all_reduce_metrics(a, b, c)
+    assert out[0] is a and float(a) == sum(1.5 + r for r in range(world))
+    assert float(b) == sum(10.0 * (r + 1) for r in range(world)) and float(c) == 3.0 * world

@@ -21,7 +21,7 @@ def _spawn(case, tmp_path, world=2, backend="gloo"):
 
 
 CASES = ["mean_gradient", "parity_with_stock_ddp", "clip_value_before_aggregation", "clip_norm_before_aggregation",
-         "no_sync_accumulation", "fault_containment", "checkpoint_rank0", "accelerator", "fused_adam_in_backward_is_bitwise"]
+         "no_sync_accumulation", "fault_containment", "checkpoint_rank0", "accelerator", "fused_adam_in_backward_is_bitwise", "metrics_one_collective"]
 
 
 @pytest.mark.parametrize("case", CASES)

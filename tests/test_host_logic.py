@@ -302,3 +302,70 @@ def test_space_to_depth_geometry_and_opt_in(monkeypatch):
     monkeypatch.setenv("B200DDP_CONV1_S2D", "1")
     assert bnn._use_s2d(3, 11, 11, 4)
     assert not bnn._use_s2d(64, 5, 5, 1) and not bnn._use_s2d(16, 11, 11, 4)     # stride 1 / too many channels
+
+
+# ---- round 2 host logic ----------------------------------------------------------------------------------------
+def test_convert_sync_batchnorm_folds_relu_and_leaves_no_eager_activation():
+    import b200ddp
+    from b200ddp import nn as bnn
+    from b200ddp.models import AlexNet
+    m = b200ddp.SyncBatchNorm.convert_sync_batchnorm(AlexNet(bn=True))
+    kinds = [type(l).__name__ for l in m.features]
+    assert "ReLU" not in kinds and "MaxPool2d" not in kinds and kinds.count("SyncBatchNorm") == 5
+    assert all(l.fuse_relu for l in m.features if isinstance(l, bnn.SyncBatchNorm))
+    assert all(not l.relu for l in m.features if isinstance(l, bnn.ReLUMaxPool2d))      # the ReLU moved into the BN kernels
+    again = b200ddp.SyncBatchNorm.convert_sync_batchnorm(m)                              # idempotent
+    assert [type(l).__name__ for l in again.features] == kinds
+
+
+def test_checkpoint_round_trip_on_cpu_keeps_reference_file_format(tmp_path):
+    """AsyncCheckpointer / load_checkpoint on a CPU model (no arena, no side stream): the primary file is what
+    torch.save(model.state_dict()) of the reference writes (:217-221); the side-car restores Adam and the sampler."""
+    import b200ddp
+    torch.manual_seed(0)
+    net = torch.nn.Sequential(torch.nn.Linear(6, 5), torch.nn.ReLU(), torch.nn.Linear(5, 3))
+    opt = b200ddp.optim.Adam(net.parameters(), lr=3e-3)
+    ds = torch.utils.data.TensorDataset(torch.arange(20))
+    sampler = b200ddp.DistributedSampler(ds, num_replicas=2, rank=1, shuffle=True, seed=5)
+    sampler.set_epoch(7)
+    x, y = torch.randn(4, 6), torch.tensor([0, 1, 2, 0])
+    for _ in range(2):
+        opt.zero_grad()
+        torch.nn.functional.cross_entropy(net(x), y).backward()
+        opt.step()
+    path = str(tmp_path / "ckpt_5.pt")
+    ck = b200ddp.AsyncCheckpointer(net, optimizer=opt, sampler=sampler)
+    ck.save(path, epoch=5, extra={"note": "x"})
+    ck.wait()
+    sd = torch.load(path, map_location="cpu")
+    assert list(sd) == list(net.state_dict()) and all(torch.equal(sd[k], v) for k, v in net.state_dict().items())
+    net2 = torch.nn.Sequential(torch.nn.Linear(6, 5), torch.nn.ReLU(), torch.nn.Linear(5, 3))
+    opt2 = b200ddp.optim.Adam(net2.parameters(), lr=1.0)
+    sampler2 = b200ddp.DistributedSampler(ds, num_replicas=2, rank=1, shuffle=True, seed=0)
+    info = b200ddp.load_checkpoint(path, net2, opt2, sampler2)
+    assert info == {"epoch": 5, "extra": {"note": "x"}} and list(sampler2) == list(sampler)
+    assert opt2.param_groups[0]["lr"] == 3e-3
+    for a, b in ((net, opt), (net2, opt2)):
+        b.zero_grad()
+        torch.nn.functional.cross_entropy(a(x), y).backward()
+        b.step()
+    for p, q in zip(net.parameters(), net2.parameters()):
+        assert torch.equal(p, q)
+
+
+def test_engine_applies_only_to_the_standard_cuda_tf32_model():
+    from b200ddp import engine
+    from b200ddp.models import AlexNet
+    x = torch.zeros(2, 3, 224, 224)
+    assert not engine.applicable(AlexNet(), x)                      # CPU tensors: never
+    assert engine.enabled()
+
+
+def test_gpu_transform_coefficient_table_shape():
+    import ctypes
+    L = _lib.load()
+    tab = (ctypes.c_int * (5 * 224))()
+    assert L.b200ddp_resize_coeffs(32, 224, tab) == 0
+    t = list(tab)
+    assert all(1 <= c <= 3 for c in t[224:448]) and t[0] == 0 and t[223] <= 31
+    assert all(sum(t[448 + 3 * i:451 + 3 * i]) in range((1 << 22) - 2, (1 << 22) + 3) for i in range(224))   # weights sum to 1.0
