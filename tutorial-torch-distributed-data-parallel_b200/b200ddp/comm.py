@@ -56,11 +56,10 @@ class NativeComm:
     def small_collective(self, send: torch.Tensor, out: torch.Tensor, sum_mode: bool, scale: float = 1.0) -> bool:
         """SyncBatchNorm-sized all-gather (out [world, n]) or rank-ordered sum (out [n]) as one kernel over peer memory
         (b200ddp_comm_small_collective). False = peer path unavailable, nothing was launched: use NCCL."""
-        # measured (DESIGN.md section 8): the peer kernel wins at 2 ranks (3.91 -> 3.72 ms/step of AlexNet-BN); at 8 ranks
-        # that model is bound by host-side stragglers and NCCL's collectives measured faster (3.97 vs 4.64 ms)
-        want = os.environ.get("B200DDP_SMALL_COLLECTIVES", "auto")
-        if want == "auto":
-            want = "own" if self.world <= 2 else "nccl"
+        # B200DDP_SMALL_COLLECTIVES=nccl selects NCCL's collectives instead (DESIGN.md section 8: at 2 ranks the peer kernel
+        # is the faster one, 3.91 -> 3.72 ms/step of AlexNet-BN; at 8 ranks that model's step time is set by host-side
+        # stragglers and varies more from run to run than the two implementations differ)
+        want = os.environ.get("B200DDP_SMALL_COLLECTIVES", "own")
         if self._small_ok is False or send.numel() > 2048 or want != "own":
             return False
         if send.data_ptr() % 16:
