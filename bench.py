@@ -176,8 +176,13 @@ def _ref_ddp_worker(rank, world, port, batch, steps, warmup, hidden, threads, ou
     import torch.distributed as dist
     from torch.nn.parallel import DistributedDataParallel as DDP
     from oracle import reference_loop as rl
-    for k in ("RANK", "WORLD_SIZE", "LOCAL_RANK", "LOCAL_WORLD_SIZE", "GROUP_RANK", "TORCHELASTIC_RUN_ID"):
-        os.environ.pop(k, None)
+    # this process was spawned from a torchrun worker: drop the launcher's rendezvous environment, in particular
+    # TORCHELASTIC_USE_AGENT_STORE, which would make BOTH ranks TCP-store clients of a server nobody runs
+    for k in list(os.environ):
+        if k.startswith("TORCHELASTIC") or k in ("RANK", "WORLD_SIZE", "LOCAL_RANK", "LOCAL_WORLD_SIZE", "GROUP_RANK",
+                                                 "GROUP_WORLD_SIZE", "ROLE_RANK", "ROLE_WORLD_SIZE", "ROLE_NAME",
+                                                 "MASTER_ADDR", "MASTER_PORT"):
+            os.environ.pop(k, None)
     torch.set_num_threads(threads)
     dist.init_process_group("gloo", init_method=f"tcp://127.0.0.1:{port}", rank=rank, world_size=world)
     model = DDP(rl.make_model(seed=1234, hidden=hidden))
