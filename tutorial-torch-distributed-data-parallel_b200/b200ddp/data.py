@@ -157,7 +157,8 @@ class DeviceLoader:
             x, y = self._dev_x[slot][:n], self._dev_y[slot][:n]
             if self.transform is not None:
                 x = self.transform(x, self._dev_f[slot][:n] if self.transform.train else None)
-                self._consumed[slot].record(main)    # the staging buffers are free once the transform has read them
+                y = y.clone()                        # the labels leave the staging buffer too (the loss reads them later)
+                self._consumed[slot].record(main)    # the staging buffers are free once transform and clone have read them
                 yield x, y
             else:
                 yield x, y
