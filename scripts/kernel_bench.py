@@ -108,6 +108,20 @@ for (N, K, tag) in ((4096, 9216, "FC1"), (4096, 4096, "FC2")):
            wbytes + 4.0 * B * (N + K), fl)
     timeit(f"gate_bias_bwd {tag}", lambda: chk(L.b200ddp_gate_bias_bwd(dz.data_ptr(), gate.data_ptr(), 0.5, y.data_ptr(), db.data_ptr(), B, N, 0,
                                                                       st()), "gate"), 9.0 * B * N)
+    # yardstick only (never on the product path): the library GEMMs stock torch would run for the same three products,
+    # without the fused epilogues - cuBLAS fp32 (the reference's Linear numerics) and cuBLAS TF32
+    for tf32 in (False, True):
+        def lib(fn, tf32=tf32):
+            def run():
+                old = torch.backends.cuda.matmul.allow_tf32
+                torch.backends.cuda.matmul.allow_tf32 = tf32
+                fn()
+                torch.backends.cuda.matmul.allow_tf32 = old
+            return run
+        kind = "tf32" if tf32 else "fp32"
+        timeit(f"cublas {kind} matmul fwd {tag} (yardstick)", lib(lambda: torch.matmul(x, w.t(), out=y)), wbytes + 4.0 * B * (N + K), fl)
+        timeit(f"cublas {kind} matmul dx {tag} (yardstick)", lib(lambda: torch.matmul(dz, w, out=dx)), wbytes + 4.0 * B * (N + K), fl)
+        timeit(f"cublas {kind} matmul dw {tag} (yardstick)", lib(lambda: torch.matmul(dz.t(), x, out=dw)), wbytes + 4.0 * B * (N + K), fl)
     del x, w, dw, ws
 
 # ---- head + loss ---------------------------------------------------------------------------------------------------------
