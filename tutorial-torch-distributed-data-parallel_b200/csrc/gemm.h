@@ -65,8 +65,10 @@ int conv1_wgrad_launch(const float* x, const float* dy, float* dw, int Nb, int C
 
 // 128-row sub-tiles per CTA that tf32_gemm_launch uses for an M x N x R problem. The kernel supports 2 (two TMEM
 // accumulators sharing one B tile, parity-tested), but on the classifier GEMMs it measured SLOWER than 1
-// (FC1 forward 57 vs 50 us, dX 53 vs 47 us on B200): those kernels are bound by the per-SM TMA fill rate
-// (~26 B/clk/SM whatever the tile shape), not by L2->SM traffic, so fewer, fatter CTAs only lose parallelism.
+// (FC1 forward 57 vs 50 us, dX 53 vs 47 us on B200). ncu (profiles/r02_gemm_ncu_summary.md): at 1 the weight stream runs
+// at 0.71 of the measured HBM copy rate with one CTA per SM and L2 at 41 % of its throughput although every CTA re-reads
+// the activation tile (L2->SM bytes = 2x the weight bytes) - L2->SM traffic is not the limiter, the number of SMs that
+// stream is (128 / 144 CTAs on 148 SMs), and fewer, fatter CTAs only lose parallelism.
 inline int tf32_row_subtiles(int M, int R) { (void)M; (void)R; return 1; }
 
 // Number of K splits tf32_gemm_launch will really use for a request (no empty splits).
