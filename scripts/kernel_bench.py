@@ -108,6 +108,14 @@ for (N, K, tag) in ((4096, 9216, "FC1"), (4096, 4096, "FC2")):
            wbytes + 4.0 * B * (N + K), fl)
     timeit(f"gate_bias_bwd {tag}", lambda: chk(L.b200ddp_gate_bias_bwd(dz.data_ptr(), gate.data_ptr(), 0.5, y.data_ptr(), db.data_ptr(), B, N, 0,
                                                                       st()), "gate"), 9.0 * B * N)
+    for pers, stg, epi in (("1", "3", "8"), ("1", "3", "16"), ("1", "2", "16"), ("1", "6", "16"), ("0", "6", "8")):
+        os.environ["B200DDP_GEMM_PERSISTENT"], os.environ["B200DDP_GEMM_PERS_STAGES"] = pers, stg
+        os.environ["B200DDP_GEMM_PERS_EPI"] = epi
+        timeit(f"gemm linear_bwd_dw {tag} mode1 persistent={pers} stages={stg} epilogue warps={epi}", lambda: chk(
+            L.b200ddp_linear_bwd_dw(dz.data_ptr(), x.data_ptr(), dw.data_ptr(), None, B, N, K, 1, 0, st()), "dw"),
+            wbytes + 4.0 * B * (N + K), fl)
+    for k in ("B200DDP_GEMM_PERSISTENT", "B200DDP_GEMM_PERS_STAGES", "B200DDP_GEMM_PERS_EPI"):
+        os.environ.pop(k, None)
     # yardstick only (never on the product path): the library GEMMs stock torch would run for the same three products,
     # without the fused epilogues - cuBLAS fp32 (the reference's Linear numerics) and cuBLAS TF32
     for tf32 in (False, True):

@@ -272,6 +272,29 @@ def test_linear_fc1_full_size_against_fp64(mode):
     assert torch.equal(y2, y1 * 2)
 
 
+@pytest.mark.parametrize("stages,epi", [(6, 8), (3, 8), (3, 16), (6, 16)])
+@pytest.mark.parametrize("B,N,K", [(128, 4096, 9216), (128, 4096, 4096), (100, 2100, 2500), (13, 4096, 4096)])
+def test_linear_dw_persistent_kernel_is_bit_identical_to_the_tile_kernel(monkeypatch, stages, epi, B, N, K):
+    """Same k-blocks in the same order into the same accumulator layout: the persistent CTAs (two TMEM accumulators,
+    ring running across tile boundaries) must reproduce the one-tile-per-CTA kernel bit for bit, tails included."""
+    torch.manual_seed(B + N)
+    x = torch.randn(B, K, device=DEV)
+    dz = torch.randn(B, N, device=DEV)
+    out = {}
+    for tag, env in (("tile", "0"), ("persistent", "1")):
+        monkeypatch.setenv("B200DDP_GEMM_PERSISTENT", env)
+        monkeypatch.setenv("B200DDP_GEMM_PERS_STAGES", str(stages))
+        monkeypatch.setenv("B200DDP_GEMM_PERS_EPI", str(epi))
+        dw = torch.full((N, K), float("nan"), device=DEV)
+        for _ in range(2):                                   # twice: barrier phases and accumulators start clean again
+            call("b200ddp_linear_bwd_dw", dz.data_ptr(), x.data_ptr(), dw.data_ptr(), None, B, N, K, 1, 0, st())
+        torch.cuda.synchronize()
+        out[tag] = dw
+    assert torch.equal(out["tile"], out["persistent"])
+    dw64 = dz.double().T @ x.double()
+    assert float((out["persistent"].double() - dw64).abs().max() / dw64.abs().max()) < TOL[1] * 2
+
+
 def test_head_small_n_against_oracle():
     rng = np.random.default_rng(3)
     for B, K in ((128, 4096), (106, 4096), (7, 33)):

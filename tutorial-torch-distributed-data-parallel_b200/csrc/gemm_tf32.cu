@@ -22,6 +22,7 @@
 #include <cuda.h>
 #include <cudaTypedefs.h>
 
+#include <cstdlib>
 #include <mutex>
 
 namespace b200 {
@@ -160,6 +161,159 @@ tf32_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 }
 
 // ------------------------------------------------------------------------------------------------
+// Persistent variant for problems with MANY output tiles and a SHORT reduction (dW of the Linear layers: R = batch, so
+// a tile is 4 k-blocks and 64 KB of output; FC1 has 2304 of them). One CTA per SM walks tiles blockIdx.x, +gridDim.x, ..:
+// the TMA ring runs ahead across tile boundaries and two TMEM accumulators alternate, so the loads and MMAs of tile
+// i+1 run while eight epilogue warps store tile i. In the one-tile-per-CTA kernel above those three phases are serial
+// per CTA (profiles/r02_gemm_ncu_summary.md: half of all warp samples wait for another phase of the same CTA).
+// Raw accumulator store only (no split-K, no fused epilogue).
+// ------------------------------------------------------------------------------------------------
+// EPIW epilogue warps = 4 TMEM lane quarters x EPIW/4 column parts; MINB CTAs per SM (register cap for the compiler).
+template <int BN, int EPIW, int MINB>
+__global__ void __launch_bounds__(64 + 32 * EPIW, MINB)
+tf32_gemm_persistent_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, KParams p,
+                            int m_tiles, int tiles) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  constexpr uint32_t A_BYTES = BM * BK * 4;
+  constexpr uint32_t B_BYTES = BN * BK * 4;
+  constexpr uint32_t STAGE_BYTES = A_BYTES + B_BYTES;
+  constexpr uint32_t TMEM_COLS = 2 * BN;
+  const int stages = p.stages;
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + (size_t)stages * STAGE_BYTES);
+  uint64_t* empty_bar = full_bar + stages;
+  uint64_t* d_full = empty_bar + stages;         // [2] MMA -> epilogue
+  uint64_t* d_empty = d_full + 2;                // [2] epilogue -> MMA
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(d_empty + 2);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int nkb = (p.R + BK - 1) / BK;
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < stages; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    for (int a = 0; a < 2; ++a) {
+      mbar_init(&d_full[a], 1);
+      mbar_init(&d_empty[a], 32 * EPIW);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmA) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmB) : "memory");
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, TMEM_COLS);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  const int my_tiles = ((int)blockIdx.x < tiles) ? (tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      // ---------------- TMA producer: the ring does not know about tile boundaries ----------------
+      int s = 0;
+      uint32_t ph = 0;
+      for (int i = 0; i < my_tiles; ++i) {
+        const int tile = (int)blockIdx.x + i * (int)gridDim.x;
+        const int nt = tile / m_tiles, mt = tile - nt * m_tiles;   // neighbouring CTAs share the B tile in L2
+        const int m0 = mt * BM, n0 = nt * BN;
+        for (int kb = 0; kb < nkb; ++kb) {
+          mbar_wait(&empty_bar[s], ph ^ 1u);
+          mbar_arrive_expect_tx(&full_bar[s], STAGE_BYTES);
+          uint8_t* sa = smem + (size_t)s * STAGE_BYTES;
+          uint8_t* sb = sa + A_BYTES;
+          const int r0 = kb * BK;
+          if (!p.a_mn) {
+            tma_load_2d(sa, &tmA, &full_bar[s], r0, m0);
+          } else {
+#pragma unroll
+            for (int j = 0; j < BM / 32; ++j) tma_load_2d(sa + j * 4096, &tmA, &full_bar[s], m0 + 32 * j, r0);
+          }
+          if (!p.b_mn) {
+            tma_load_2d(sb, &tmB, &full_bar[s], r0, n0);
+          } else {
+#pragma unroll
+            for (int j = 0; j < BN / 32; ++j) tma_load_2d(sb + j * 4096, &tmB, &full_bar[s], n0 + 32 * j, r0);
+          }
+          if (++s == stages) { s = 0; ph ^= 1u; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ---------------- MMA issuer: all 32 lanes walk the loop, one elected lane issues ----------------
+    const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)p.a_mn << 15) | ((uint32_t)p.b_mn << 16)
+                           | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+    const OperandDesc a = p.a_mn ? operand_mn_major() : operand_k_major();
+    const OperandDesc b = p.b_mn ? operand_mn_major() : operand_k_major();
+    const uint32_t smem_saddr = smem_u32(smem);
+    const uint32_t a_lo0 = ((smem_saddr & 0x3FFFFu) >> 4) | ((a.lbo >> 4) << 16);
+    const uint32_t b_lo0 = (((smem_saddr + A_BYTES) & 0x3FFFFu) >> 4) | ((b.lbo >> 4) << 16);
+    const uint32_t a_hi = (a.sbo >> 4) | (1u << 14) | (a.layout_type << 29);
+    const uint32_t b_hi = (b.sbo >> 4) | (1u << 14) | (b.layout_type << 29);
+    const uint32_t a_step = a.k_advance >> 4, b_step = b.k_advance >> 4, stage_step = STAGE_BYTES >> 4;
+    const uint32_t full0 = smem_u32(&full_bar[0]), empty0 = smem_u32(&empty_bar[0]);
+    uint32_t a_lo = a_lo0, b_lo = b_lo0, fb = full0, eb = empty0, ph = 0;
+    int s = 0;
+#pragma unroll 1
+    for (int i = 0; i < my_tiles; ++i) {
+      const int acc = i & 1;
+      mbar_wait(&d_empty[acc], (((uint32_t)i >> 1) & 1u) ^ 1u);      // the epilogue has drained this accumulator
+      tc_fence_after();
+      const uint32_t d_addr = tmem_base + (uint32_t)(acc * BN);
+#pragma unroll 1
+      for (int kb = 0; kb < nkb; ++kb) {
+        mbar_wait_addr(fb, ph);
+        tc_fence_after();
+        if (elect_one()) {
+#pragma unroll
+          for (int k = 0; k < BK / UMMA_K; ++k)
+            umma_tf32_lohi(d_addr, a_lo + k * a_step, a_hi, b_lo + k * b_step, b_hi, idesc, (kb | k) ? 1u : 0u);
+          umma_commit_addr(eb);
+          if (kb == nkb - 1) umma_commit(&d_full[acc]);
+        }
+        __syncwarp();
+        if (++s == stages) {
+          s = 0; ph ^= 1u; a_lo = a_lo0; b_lo = b_lo0; fb = full0; eb = empty0;
+        } else {
+          a_lo += stage_step; b_lo += stage_step; fb += 8u; eb += 8u;
+        }
+      }
+    }
+  } else {
+    // ---------------- epilogue: 4 TMEM lane quarters x EPIW/4 column parts ----------------
+    constexpr int PART = BN / (EPIW / 4);                  // columns per warp: 64 or 32
+    const int q = warp & 3;
+    const int part = (warp - 2) >> 2;
+#pragma unroll 1
+    for (int i = 0; i < my_tiles; ++i) {
+      const int tile = (int)blockIdx.x + i * (int)gridDim.x;
+      const int nt = tile / m_tiles, mt = tile - nt * m_tiles;
+      const int m = mt * BM + q * 32 + lane;
+      const int n_base = nt * BN + part * PART;
+      const int acc = i & 1;
+      mbar_wait(&d_full[acc], ((uint32_t)i >> 1) & 1u);
+      tc_fence_after();
+#pragma unroll 1
+      for (int c = 0; c < PART; c += 32) {
+        uint32_t r[32];
+        tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * BN + part * PART + c), r);
+        if (m < p.M) {
+          float* dst = p.out + (long long)(n_base + c) * p.ldo + m;
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            if (n_base + c + j < p.N) dst[(long long)j * p.ldo] = __uint_as_float(r[j]);
+        }
+      }
+      tc_fence_before();
+      mbar_arrive(&d_empty[acc]);
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem_base, TMEM_COLS);
+}
+
+// ------------------------------------------------------------------------------------------------
 // host side
 // ------------------------------------------------------------------------------------------------
 }  // namespace
@@ -230,6 +384,12 @@ int tma_map_nd(CUtensorMap* map, const float* base, int rank, const long long* g
 
 namespace {
 
+// B200DDP_GEMM_PERSISTENT=0 keeps every GEMM on the one-tile-per-CTA kernel (read per call: a benchmark flips it)
+inline bool tf32_persistent_mode() {
+  const char* e = getenv("B200DDP_GEMM_PERSISTENT");
+  return e ? (e[0] != '0') : true;
+}
+
 template <int BN, bool EPI, int RS>
 int launch_bn(const CUtensorMap& tmA, const CUtensorMap& tmB, const KParams& p, cudaStream_t stream) {
   const size_t stage_bytes = (size_t)(BM * RS + BN) * BK * 4;
@@ -248,6 +408,27 @@ int launch_bn(const CUtensorMap& tmA, const CUtensorMap& tmB, const KParams& p, 
   if (e != cudaSuccess) {
     set_error("tf32_gemm_kernel<%d> launch (grid %d,%d,%d smem %zu) -> %s", BN, grid.x, grid.y, grid.z, smem,
               cudaGetErrorString(e));
+    return kCudaErrBase + (int)e;
+  }
+  count_launch();
+  return 0;
+}
+
+template <int BN, int EPIW, int MINB>
+int launch_persistent(const CUtensorMap& tmA, const CUtensorMap& tmB, const KParams& p, int m_tiles, int tiles, int grid,
+                      cudaStream_t stream) {
+  const size_t stage_bytes = (size_t)(BM + BN) * BK * 4;
+  const size_t smem = 1024 + (size_t)p.stages * stage_bytes + (2 * p.stages + 4) * 8 + 16;
+  static std::atomic<unsigned long long> attr_devices{0};
+  cudaError_t e = ensure_max_dyn_smem(tf32_gemm_persistent_kernel<BN, EPIW, MINB>, attr_devices);
+  if (e != cudaSuccess) {
+    set_error("cudaFuncSetAttribute(tf32_gemm_persistent_kernel) -> %s", cudaGetErrorString(e));
+    return kCudaErrBase + (int)e;
+  }
+  tf32_gemm_persistent_kernel<BN, EPIW, MINB><<<grid, 64 + 32 * EPIW, smem, stream>>>(tmA, tmB, p, m_tiles, tiles);
+  e = cudaGetLastError();
+  if (e != cudaSuccess) {
+    set_error("tf32_gemm_persistent_kernel launch (grid %d smem %zu) -> %s", grid, smem, cudaGetErrorString(e));
     return kCudaErrBase + (int)e;
   }
   count_launch();
@@ -292,6 +473,29 @@ int tf32_gemm_launch(const float* A, long long lda, int a_mn, const float* B, lo
     return kInvalidArg;
   }
   const bool epi = p.splits == 1 && (ep.bias || ep.relu || ep.dropout || ep.gate);
+  {
+    // many tiles, short reduction, raw store: persistent CTAs (see tf32_gemm_persistent_kernel)
+    const int m_tiles = (M + BM - 1) / BM, n_tiles = (N + 127) / 128;
+    const long long tiles = (long long)m_tiles * n_tiles;
+    const int sms = sm_budget() > 0 ? sm_budget() : num_sms();
+    if (tf32_persistent_mode() && p.splits == 1 && !epi && BN == 128 && total_kb <= 8 && tiles >= 2ll * sms &&
+        tiles < (1ll << 30)) {
+      const char* st_env = getenv("B200DDP_GEMM_PERS_STAGES");
+      int st = st_env ? atoi(st_env) : 3;
+      if (st < 2) st = 2;
+      if (st > 6) st = 6;
+      p.stages = st;
+      const int per_sm = st <= 3 ? 2 : 1;                 // 3 stages = 97 KB: two CTAs (2 x 256 TMEM columns) share an SM
+      long long grid = (long long)sms * per_sm;
+      if (grid > tiles) grid = tiles;
+      const char* ew_env = getenv("B200DDP_GEMM_PERS_EPI");
+      const int ew = ew_env ? atoi(ew_env) : 16;
+      if (ew == 16)
+        return per_sm == 2 ? launch_persistent<128, 16, 2>(tmA, tmB, p, m_tiles, (int)tiles, (int)grid, stream)
+                           : launch_persistent<128, 16, 1>(tmA, tmB, p, m_tiles, (int)tiles, (int)grid, stream);
+      return launch_persistent<128, 8, 2>(tmA, tmB, p, m_tiles, (int)tiles, (int)grid, stream);
+    }
+  }
   if (rs == 2) {
     if (BN == 128) return epi ? launch_bn<128, true, 2>(tmA, tmB, p, stream) : launch_bn<128, false, 2>(tmA, tmB, p, stream);
     return epi ? launch_bn<64, true, 2>(tmA, tmB, p, stream) : launch_bn<64, false, 2>(tmA, tmB, p, stream);
