@@ -384,10 +384,14 @@ int tma_map_nd(CUtensorMap* map, const float* base, int rank, const long long* g
 
 namespace {
 
-// B200DDP_GEMM_PERSISTENT=0 keeps every GEMM on the one-tile-per-CTA kernel (read per call: a benchmark flips it)
+// Whether the persistent kernel takes the short-reduction raw-store GEMMs. Default: when no SMs are set aside for a
+// resident collective (b200ddp_set_sm_budget) - its CTAs stay on their SMs for the whole kernel, and that has only been
+// measured next to the all-reduce kernel's SM-owning CTAs on one GPU. B200DDP_GEMM_PERSISTENT=1 / 0 forces it on / off
+// (read per call: a benchmark flips it).
 inline bool tf32_persistent_mode() {
   const char* e = getenv("B200DDP_GEMM_PERSISTENT");
-  return e ? (e[0] != '0') : true;
+  if (e && e[0]) return e[0] != '0';
+  return sm_budget() >= num_sms();
 }
 
 template <int BN, bool EPI, int RS>
