@@ -22,10 +22,9 @@ With CPU tensors (gloo) the same host logic runs with torch ops in place of the 
 from __future__ import annotations
 
 import ctypes
+import os
 import weakref
 from typing import List, Optional
-
-import os
 
 import torch
 import torch.distributed as dist
@@ -114,9 +113,9 @@ class Reducer:
                 comm.set_algo("ring")
             _comm_mod.reserve_sms_for_nccl(self.algo != "own")
             if self.algo == "own" and big:       # 1024-thread CTAs own their SM: plan the compute grids around them
-                import ctypes
-                n = ctypes.c_int(148)
-                _lib.load().b200ddp_device_info(arena.device.index or 0, ctypes.byref(n), None, None)
+                n = ctypes.c_int(0)
+                _lib.check(_lib.load().b200ddp_device_info(_lib.dev_index(arena.g_flat), ctypes.byref(n), None, None),
+                           "device_info")
                 _lib.load().b200ddp_set_sm_budget(max(16, n.value - ctas))
         self._chunk_elems = max(1, int(os.environ.get("B200DDP_AR_CHUNK_MB", "64"))) << 18      # MB -> fp32 elements
         self.pass_prescaled = False
